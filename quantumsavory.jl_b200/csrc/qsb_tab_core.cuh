@@ -1,0 +1,405 @@
+// qsb_tab_core.cuh -- the bit-sliced tableau algorithms as host+device inline functions.
+// The CUDA kernels in qsb_tab.cu are thin per-word wrappers around these; tests/cpu_emul compiles the
+// same functions with g++ to exercise the lane-masked pivot logic on 32-lane words without a GPU
+// (a debugging aid for the algorithm only -- never a product path, never timed).
+#pragma once
+#include <stdint.h>
+#include <stddef.h>
+#if defined(__CUDACC__)
+#define QSB_HD __host__ __device__ __forceinline__
+#else
+#define QSB_HD inline
+#endif
+#ifndef QSB_TAB_MAXN
+#define QSB_TAB_MAXN 32
+#endif
+#define MAXN QSB_TAB_MAXN
+
+QSB_HD uint32_t qsb_mulhi32(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+    return __umulhi(a, b);
+#else
+    return (uint32_t)(((uint64_t)a * b) >> 32);
+#endif
+}
+// Philox4x32-10; identical to the oracle's qso_draw (the "injected draw").
+QSB_HD double qsb_draw(uint64_t seed, uint64_t traj, uint64_t draw_id) {
+    uint32_t c0 = (uint32_t)traj, c1 = (uint32_t)(traj >> 32), c2 = (uint32_t)draw_id, c3 = (uint32_t)(draw_id >> 32);
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+    for (int r = 0; r < 10; ++r) {
+        uint32_t h0 = qsb_mulhi32(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+        uint32_t h1 = qsb_mulhi32(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = h1 ^ c1 ^ k0, n2 = h0 ^ c3 ^ k1;
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    uint64_t bits = ((uint64_t)c1 << 32) | c0;
+    return (double)(bits >> 11) * (1.0 / 9007199254740992.0);
+}
+
+struct TabView {
+    uint32_t* p; size_t W; size_t w; int n; int S;
+    QSB_HD uint32_t ld(int plane) const { return p[(size_t)plane * W + w]; }
+    QSB_HD void st(int plane, uint32_t v) const { p[(size_t)plane * W + w] = v; }
+    QSB_HD int dx(int i, int c) const { return i * S + c; }
+    QSB_HD int dz(int i, int c) const { return i * S + n + c; }
+    QSB_HD int sx(int i, int c) const { return i * S + 2 * n + c; }
+    QSB_HD int sz(int i, int c) const { return i * S + 3 * n + c; }
+    QSB_HD int sg(int i) const { return i * S + 4 * n; }
+    QSB_HD int ac(int i) const { return i * S + 4 * n + 1; }
+};
+QSB_HD TabView make_view(uint32_t* p, size_t W, size_t w, int n) { TabView v; v.p = p; v.W = W; v.w = w; v.n = n; v.S = 4 * n + 2; return v; }
+
+
+// dst row (planes x0.., z0.., optional sign plane) <- src * dst on lanes m, src given in registers/local
+// arrays.  The exponent of i is tracked in a bit-sliced 2-bit counter (lo,hi); rows always commute here,
+// so lo ends at 0 and the sign flip is hi.
+QSB_HD void row_mul(const TabView& v, int x0, int z0, int sgplane, uint32_t m,
+                                        const uint32_t* sx, const uint32_t* sz, uint32_t ssign) {
+    if (m == 0) return;
+    uint32_t lo = 0, hi = 0;
+    for (int c = 0; c < v.n; ++c) {
+        uint32_t x1 = sx[c], z1 = sz[c];
+        if ((x1 | z1) == 0) continue;
+        uint32_t x2 = v.ld(x0 + c), z2 = v.ld(z0 + c);
+        uint32_t anti = (x1 & z2) ^ (z1 & x2);
+        // g = -1 for (X,Z), (Y,X), (Z,Y); +1 for the cyclic pairs
+        uint32_t neg = anti & ((x1 & ~z1 & ~x2) | (x1 & z1 & ~z2) | (~x1 & x2 & z2));
+        hi ^= (lo & anti) ^ neg;
+        lo ^= anti;
+        v.st(x0 + c, x2 ^ (x1 & m));
+        v.st(z0 + c, z2 ^ (z1 & m));
+    }
+    if (sgplane >= 0) v.st(sgplane, v.ld(sgplane) ^ ((ssign ^ hi) & m));
+}
+
+struct Analysis {
+    uint32_t acS[MAXN], acD[MAXN], act[MAXN], piv[MAXN];
+    uint32_t found;
+};
+
+// anticommutation words of every row with the Pauli (px,pz) and lane-wise pivot choice:
+// first active stabilizer that anticommutes, else an inactive (logical) row that anticommutes.
+QSB_HD void analyze(const TabView& v, uint32_t px, uint32_t pz, Analysis& A, uint32_t* pivD) {
+    int n = v.n;
+    for (int i = 0; i < n; ++i) {
+        uint32_t s = 0, d = 0;
+        for (int c = 0; c < n; ++c) {
+            if ((pz >> c) & 1) { s ^= v.ld(v.sx(i, c)); d ^= v.ld(v.dx(i, c)); }
+            if ((px >> c) & 1) { s ^= v.ld(v.sz(i, c)); d ^= v.ld(v.dz(i, c)); }
+        }
+        A.acS[i] = s; A.acD[i] = d; A.act[i] = v.ld(v.ac(i));
+    }
+    uint32_t found = 0;
+    for (int i = 0; i < n; ++i) { A.piv[i] = A.acS[i] & A.act[i] & ~found; found |= A.piv[i]; }
+    for (int i = 0; i < n; ++i) { uint32_t t = A.acS[i] & ~A.act[i] & ~found; A.piv[i] |= t; found |= t; }
+    for (int i = 0; i < n; ++i) { uint32_t t = A.acD[i] & ~A.act[i] & ~found; pivD[i] = t; found |= t; }
+    A.found = found;
+}
+
+// sign (1 = minus) of the group element equal to the Pauli bits on the lanes where it is determined:
+// product of the active S_i whose destabilizer anticommutes with P.
+QSB_HD uint32_t determined_sign(const TabView& v, const Analysis& A, uint32_t det) {
+    uint32_t accx[MAXN], accz[MAXN];
+    int n = v.n;
+    for (int c = 0; c < n; ++c) { accx[c] = 0; accz[c] = 0; }
+    uint32_t lo = 0, hi = 0, sg = 0;
+    for (int i = 0; i < n; ++i) {
+        uint32_t m = A.acD[i] & A.act[i] & det;
+        if (m == 0) continue;
+        for (int c = 0; c < n; ++c) {
+            uint32_t x1 = v.ld(v.sx(i, c)) & m, z1 = v.ld(v.sz(i, c)) & m;
+            uint32_t x2 = accx[c], z2 = accz[c];
+            uint32_t anti = (x1 & z2) ^ (z1 & x2);
+            uint32_t neg = anti & ((x1 & ~z1 & ~x2) | (x1 & z1 & ~z2) | (~x1 & x2 & z2));
+            hi ^= (lo & anti) ^ neg;
+            lo ^= anti;
+            accx[c] = x2 ^ x1; accz[c] = z2 ^ z1;
+        }
+        sg ^= v.ld(v.sg(i)) & m;
+    }
+    return (sg ^ hi) & det;
+}
+
+// Full projection update.  Returns in A.piv the (lane-wise one-hot) pair whose S row now holds +/-P.
+// random lanes (A.found): S_piv <- (-1)^rbit P, D_piv <- old S_piv, other anticommuting rows *= old S_piv.
+// determined lanes: outcome from determined_sign; when `settle` the pair of the first contributing
+// destabilizer is rewritten so that S_piv = +/-P as well (needed before a qubit is removed).
+QSB_HD uint32_t project_update(const TabView& v, uint32_t px, uint32_t pz, uint32_t rbits, bool settle, Analysis& A) {
+    int n = v.n;
+    uint32_t pivD[MAXN];
+    analyze(v, px, pz, A, pivD);
+    uint32_t found = A.found, det = ~found;
+    uint32_t dsign = determined_sign(v, A, det);
+    // logical-row pivots found on a D row: exchange D_i and S_i there (both are logical operators)
+    for (int i = 0; i < n; ++i) {
+        uint32_t m = pivD[i];
+        if (m == 0) continue;
+        for (int c = 0; c < n; ++c) {
+            uint32_t a = v.ld(v.dx(i, c)), b = v.ld(v.sx(i, c)), t = (a ^ b) & m;
+            v.st(v.dx(i, c), a ^ t); v.st(v.sx(i, c), b ^ t);
+            a = v.ld(v.dz(i, c)); b = v.ld(v.sz(i, c)); t = (a ^ b) & m;
+            v.st(v.dz(i, c), a ^ t); v.st(v.sz(i, c), b ^ t);
+        }
+        v.st(v.sg(i), v.ld(v.sg(i)) & ~m);
+        uint32_t t = (A.acS[i] ^ A.acD[i]) & m;
+        A.acS[i] ^= t; A.acD[i] ^= t;
+        A.piv[i] |= m;
+    }
+    if (found) {
+        uint32_t pvx[MAXN], pvz[MAXN], pvs = 0;
+        for (int c = 0; c < n; ++c) { pvx[c] = 0; pvz[c] = 0; }
+        for (int i = 0; i < n; ++i) {
+            uint32_t m = A.piv[i];
+            if (m == 0) continue;
+            for (int c = 0; c < n; ++c) { pvx[c] |= v.ld(v.sx(i, c)) & m; pvz[c] |= v.ld(v.sz(i, c)) & m; }
+            pvs |= v.ld(v.sg(i)) & m;
+        }
+        for (int i = 0; i < n; ++i) {
+            row_mul(v, v.sx(i, 0), v.sz(i, 0), v.sg(i), A.acS[i] & found & ~A.piv[i], pvx, pvz, pvs);
+            row_mul(v, v.dx(i, 0), v.dz(i, 0), -1, A.acD[i] & found & ~A.piv[i], pvx, pvz, pvs);
+        }
+        for (int i = 0; i < n; ++i) {
+            uint32_t m = A.piv[i];
+            if (m == 0) continue;
+            for (int c = 0; c < n; ++c) {
+                uint32_t pxc = ((px >> c) & 1) ? 0xFFFFFFFFu : 0u, pzc = ((pz >> c) & 1) ? 0xFFFFFFFFu : 0u;
+                v.st(v.dx(i, c), (v.ld(v.dx(i, c)) & ~m) | (pvx[c] & m));
+                v.st(v.dz(i, c), (v.ld(v.dz(i, c)) & ~m) | (pvz[c] & m));
+                v.st(v.sx(i, c), (v.ld(v.sx(i, c)) & ~m) | (pxc & m));
+                v.st(v.sz(i, c), (v.ld(v.sz(i, c)) & ~m) | (pzc & m));
+            }
+            v.st(v.sg(i), (v.ld(v.sg(i)) & ~m) | (rbits & m));
+            A.act[i] |= m;
+            v.st(v.ac(i), A.act[i]);
+        }
+    }
+    if (settle && det) {
+        // choose p = first active pair whose D anticommutes with P; D_i <- D_i D_p for the others; S_p <- +/-P
+        uint32_t pd[MAXN], fd = 0;
+        for (int i = 0; i < n; ++i) { pd[i] = A.acD[i] & A.act[i] & det & ~fd; fd |= pd[i]; }
+        uint32_t dpx[MAXN], dpz[MAXN];
+        for (int c = 0; c < n; ++c) { dpx[c] = 0; dpz[c] = 0; }
+        for (int i = 0; i < n; ++i) {
+            if (pd[i] == 0) continue;
+            for (int c = 0; c < n; ++c) { dpx[c] |= v.ld(v.dx(i, c)) & pd[i]; dpz[c] |= v.ld(v.dz(i, c)) & pd[i]; }
+        }
+        for (int i = 0; i < n; ++i) {
+            uint32_t m = A.acD[i] & A.act[i] & det & ~pd[i];
+            if (m) for (int c = 0; c < n; ++c) { v.st(v.dx(i, c), v.ld(v.dx(i, c)) ^ (dpx[c] & m)); v.st(v.dz(i, c), v.ld(v.dz(i, c)) ^ (dpz[c] & m)); }
+        }
+        for (int i = 0; i < n; ++i) {
+            uint32_t m = pd[i];
+            if (m == 0) continue;
+            for (int c = 0; c < n; ++c) {
+                uint32_t pxc = ((px >> c) & 1) ? 0xFFFFFFFFu : 0u, pzc = ((pz >> c) & 1) ? 0xFFFFFFFFu : 0u;
+                v.st(v.sx(i, c), (v.ld(v.sx(i, c)) & ~m) | (pxc & m));
+                v.st(v.sz(i, c), (v.ld(v.sz(i, c)) & ~m) | (pzc & m));
+            }
+            v.st(v.sg(i), (v.ld(v.sg(i)) & ~m) | (dsign & m));
+            A.piv[i] |= m;
+        }
+    }
+    return (rbits & found) | dsign;  // outcome bit per lane (1 = eigenvalue -1)
+}
+
+// drop qubit q and the pivot pair: every other row has I or the measured Pauli on q, multiplying by
+// S_piv (= +/-P_q) clears it and only touches the sign; pair n-1 moves into the pivot's slot.
+QSB_HD void remove_qubit(const TabView& v, const TabView& o, int q, const Analysis& A, uint32_t outcome, uint32_t skip_sign_fix) {
+    int n = v.n;
+    for (int i = 0; i < n; ++i) {
+        uint32_t nz = (v.ld(v.sx(i, q)) | v.ld(v.sz(i, q))) & ~A.piv[i] & ~skip_sign_fix;
+        if (nz & outcome) v.st(v.sg(i), v.ld(v.sg(i)) ^ (nz & outcome));
+    }
+    int last = n - 1;
+    for (int i = 0; i < n - 1; ++i) {
+        uint32_t m = A.piv[i];  // lanes whose pivot sits here take pair `last`
+        int cc = 0;
+        for (int c = 0; c < n; ++c) {
+            if (c == q) continue;
+            o.st(o.dx(i, cc), (v.ld(v.dx(i, c)) & ~m) | (v.ld(v.dx(last, c)) & m));
+            o.st(o.dz(i, cc), (v.ld(v.dz(i, c)) & ~m) | (v.ld(v.dz(last, c)) & m));
+            o.st(o.sx(i, cc), (v.ld(v.sx(i, c)) & ~m) | (v.ld(v.sx(last, c)) & m));
+            o.st(o.sz(i, cc), (v.ld(v.sz(i, c)) & ~m) | (v.ld(v.sz(last, c)) & m));
+            ++cc;
+        }
+        o.st(o.sg(i), (v.ld(v.sg(i)) & ~m) | (v.ld(v.sg(last)) & m));
+        o.st(o.ac(i), (v.ld(v.ac(i)) & ~m) | (v.ld(v.ac(last)) & m));
+    }
+}
+
+
+QSB_HD uint32_t lane_bits_ge_half(uint64_t seed, uint64_t traj0, size_t w, uint64_t draw_id) {
+    uint32_t r = 0;
+    for (int l = 0; l < 32; ++l) if (qsb_draw(seed, traj0 + (uint64_t)(w * 32 + l), draw_id) >= 0.5) r |= 1u << l;
+    return r;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// per-word bodies of the kernels in qsb_tab.cu
+// ---------------------------------------------------------------------------------------------
+QSB_HD void tab_init_word(uint32_t* p, size_t W, size_t w, int n, int active) {
+    TabView v = make_view(p, W, w, n);
+    for (int i = 0; i < n; ++i) {
+        for (int c = 0; c < n; ++c) {
+            v.st(v.dx(i, c), c == i ? 0xFFFFFFFFu : 0u); v.st(v.dz(i, c), 0u);
+            v.st(v.sx(i, c), 0u); v.st(v.sz(i, c), c == i ? 0xFFFFFFFFu : 0u);
+        }
+        v.st(v.sg(i), 0u);
+        v.st(v.ac(i), active ? 0xFFFFFFFFu : 0u);
+    }
+}
+
+QSB_HD void tab_tensor_word(uint32_t* out, const uint32_t* a, const uint32_t* b, size_t W, size_t w, int na, int nb) {
+    int n = na + nb;
+    TabView o = make_view(out, W, w, n), va = make_view((uint32_t*)a, W, w, na), vb = make_view((uint32_t*)b, W, w, nb);
+    for (int i = 0; i < n; ++i) {
+        bool fa = i < na;
+        int j = fa ? i : i - na;
+        for (int c = 0; c < n; ++c) {
+            bool in_a = c < na;
+            uint32_t dxv = 0, dzv = 0, sxv = 0, szv = 0;
+            if (fa && in_a) { dxv = va.ld(va.dx(j, c)); dzv = va.ld(va.dz(j, c)); sxv = va.ld(va.sx(j, c)); szv = va.ld(va.sz(j, c)); }
+            if (!fa && !in_a) { int cc = c - na; dxv = vb.ld(vb.dx(j, cc)); dzv = vb.ld(vb.dz(j, cc)); sxv = vb.ld(vb.sx(j, cc)); szv = vb.ld(vb.sz(j, cc)); }
+            o.st(o.dx(i, c), dxv); o.st(o.dz(i, c), dzv); o.st(o.sx(i, c), sxv); o.st(o.sz(i, c), szv);
+        }
+        o.st(o.sg(i), fa ? va.ld(va.sg(j)) : vb.ld(vb.sg(j)));
+        o.st(o.ac(i), fa ? va.ld(va.ac(j)) : vb.ld(vb.ac(j)));
+    }
+}
+
+struct TabGateArgs { int n, k, q[2]; uint8_t outmask[4]; uint32_t lut; };
+QSB_HD void tab_gate_word(uint32_t* p, size_t W, size_t w, const TabGateArgs& a, uint32_t m) {
+    if (m == 0) return;
+    TabView v = make_view(p, W, w, a.n);
+    int nb = 2 * a.k;
+    for (int i = 0; i < a.n; ++i) {
+        for (int half = 0; half < 2; ++half) {
+            int px[2], pz[2];
+            for (int j = 0; j < a.k; ++j) { px[j] = half ? v.sx(i, a.q[j]) : v.dx(i, a.q[j]); pz[j] = half ? v.sz(i, a.q[j]) : v.dz(i, a.q[j]); }
+            uint32_t in[4] = {0, 0, 0, 0};
+            for (int j = 0; j < a.k; ++j) { in[2 * j] = v.ld(px[j]); in[2 * j + 1] = v.ld(pz[j]); }
+            uint32_t outv[4];
+            for (int b = 0; b < nb; ++b) {
+                uint32_t o = 0;
+                for (int j = 0; j < nb; ++j) if ((a.outmask[b] >> j) & 1) o ^= in[j];
+                outv[b] = o;
+            }
+            for (int j = 0; j < a.k; ++j) {
+                v.st(px[j], (in[2 * j] & ~m) | (outv[2 * j] & m));
+                v.st(pz[j], (in[2 * j + 1] & ~m) | (outv[2 * j + 1] & m));
+            }
+            if (half && a.lut) {
+                uint32_t flip = 0;
+                for (int t = 0; t < (1 << nb); ++t) {
+                    if (!((a.lut >> t) & 1)) continue;
+                    uint32_t term = 0xFFFFFFFFu;
+                    for (int j = 0; j < nb; ++j) term &= ((t >> j) & 1) ? in[j] : ~in[j];
+                    flip |= term;
+                }
+                v.st(v.sg(i), v.ld(v.sg(i)) ^ (flip & m));
+            }
+        }
+    }
+}
+
+struct TabNoiseArgs { int n, q, np; double cum[3]; int op[3]; /* 1 X, 2 Y, 3 Z */ };
+QSB_HD void tab_noise_word(uint32_t* p, size_t W, size_t w, const TabNoiseArgs& a, uint64_t seed, uint64_t traj0, uint64_t draw_id) {
+    uint32_t fx = 0, fz = 0;  // lanes receiving a Pauli with X / Z component
+    for (int l = 0; l < 32; ++l) {
+        double r = qsb_draw(seed, traj0 + (uint64_t)(w * 32 + l), draw_id);
+        for (int i = 0; i < a.np; ++i) {
+            if (r > a.cum[i]) {
+                int P = a.op[i];
+                if (P == 1 || P == 2) fx |= 1u << l;
+                if (P == 3 || P == 2) fz |= 1u << l;
+                break;
+            }
+        }
+    }
+    if ((fx | fz) == 0) return;
+    TabView v = make_view(p, W, w, a.n);
+    for (int i = 0; i < a.n; ++i) {  // sign of S_i flips where it anticommutes with the applied Pauli
+        uint32_t flip = (v.ld(v.sx(i, a.q)) & fz) ^ (v.ld(v.sz(i, a.q)) & fx);
+        if (flip) v.st(v.sg(i), v.ld(v.sg(i)) ^ flip);
+    }
+}
+
+// project_traceout! on a tableau (a9): projectremoverand!(state, projectX!/Y!/Z!, idx).
+// returns the outcome word (bit = 1 for outcome 2); *rnd = lanes whose outcome consumed the draw.
+QSB_HD uint32_t tab_measure_word(uint32_t* in, uint32_t* out, size_t W, size_t w, int n, int q, int tx, int tz,
+                                 uint64_t seed, uint64_t traj0, uint64_t draw_id, uint32_t* rnd) {
+    TabView v = make_view(in, W, w, n), o = make_view(out, W, w, n - 1);
+    Analysis A;
+    uint32_t rbits = lane_bits_ge_half(seed, traj0, w, draw_id);
+    uint32_t outcome = project_update(v, (uint32_t)tx << q, (uint32_t)tz << q, rbits, true, A);
+    *rnd = A.found;
+    if (n > 1) remove_qubit(v, o, q, A, outcome, 0u);
+    return outcome;
+}
+
+// traceout! on a tableau (a10): the group of ptrace_q(rho) is { g in G : g|_q = I }.
+QSB_HD void tab_ptrace_word(uint32_t* in, uint32_t* out, size_t W, size_t w, int n, int q) {
+    TabView v = make_view(in, W, w, n), o = make_view(out, W, w, n - 1);
+    Analysis A;
+    uint32_t outcome = project_update(v, 0u, 1u << q, 0u, true, A);  // Z_q; the sign is forgotten on random lanes
+    uint32_t rnd = A.found;
+    if (rnd) {
+        // the other stabilizers with Z on q only survive in pairs: keep products with the first one, which is lost
+        uint32_t pj[MAXN], fj = 0;
+        for (int i = 0; i < n; ++i) { pj[i] = A.act[i] & v.ld(v.sz(i, q)) & ~A.piv[i] & rnd & ~fj; fj |= pj[i]; }
+        if (fj) {
+            uint32_t jx[MAXN], jz[MAXN], js = 0, dax[MAXN], daz[MAXN];
+            for (int c = 0; c < n; ++c) { jx[c] = 0; jz[c] = 0; dax[c] = 0; daz[c] = 0; }
+            for (int i = 0; i < n; ++i) {
+                if (pj[i] == 0) continue;
+                for (int c = 0; c < n; ++c) { jx[c] |= v.ld(v.sx(i, c)) & pj[i]; jz[c] |= v.ld(v.sz(i, c)) & pj[i]; }
+                js |= v.ld(v.sg(i)) & pj[i];
+            }
+            for (int k = 0; k < n; ++k) {
+                uint32_t mk = A.act[k] & v.ld(v.sz(k, q)) & ~A.piv[k] & ~pj[k] & fj;
+                if (mk == 0) continue;
+                for (int c = 0; c < n; ++c) { dax[c] ^= v.ld(v.dx(k, c)) & mk; daz[c] ^= v.ld(v.dz(k, c)) & mk; }
+                row_mul(v, v.sx(k, 0), v.sz(k, 0), v.sg(k), mk, jx, jz, js);
+            }
+            for (int i = 0; i < n; ++i) {
+                if (pj[i] == 0) continue;
+                for (int c = 0; c < n; ++c) { v.st(v.dx(i, c), v.ld(v.dx(i, c)) ^ (dax[c] & pj[i])); v.st(v.dz(i, c), v.ld(v.dz(i, c)) ^ (daz[c] & pj[i])); }
+                v.st(v.ac(i), v.ld(v.ac(i)) & ~pj[i]);
+            }
+        }
+    }
+    remove_qubit(v, o, q, A, outcome, rnd);
+}
+
+// force a (multi-qubit) Pauli with a given sign into the group: used to build a state from generators
+QSB_HD void tab_force_word(uint32_t* p, size_t W, size_t w, int n, uint32_t px, uint32_t pz, int sign) {
+    TabView v = make_view(p, W, w, n);
+    Analysis A;
+    project_update(v, px, pz, sign ? 0xFFFFFFFFu : 0u, false, A);
+}
+
+struct TabObsArgs { int n, k, nelem; uint32_t px[64], pz[64]; uint8_t sign[64]; };
+// Each element h of the observable's Pauli group contributes <h> in {-1,0,+1}; a single Pauli is the
+// 1-element case.  value = sum_h <h> / nelem (for a projector the signs are a character of the subgroup
+// with non-zero expectation, so the sum is |H| or 0).  Bit-sliced tallies of the +1 and -1 terms.
+QSB_HD void tab_expect_word(uint32_t* p, size_t W, size_t w, const TabObsArgs& a, uint32_t* cnt, uint32_t* cntm) {
+    TabView v = make_view(p, W, w, a.n);
+    for (int b = 0; b < 8; ++b) { cnt[b] = 0; cntm[b] = 0; }
+    Analysis A;
+    uint32_t pivD[MAXN];
+    for (int e = 0; e < a.nelem; ++e) {
+        uint32_t nonzero, neg;
+        if ((a.px[e] | a.pz[e]) == 0) { nonzero = 0xFFFFFFFFu; neg = a.sign[e] ? 0xFFFFFFFFu : 0u; }
+        else {
+            analyze(v, a.px[e], a.pz[e], A, pivD);
+            nonzero = ~A.found;
+            neg = determined_sign(v, A, nonzero) ^ (a.sign[e] ? nonzero : 0u);
+        }
+        uint32_t carry = nonzero & ~neg;
+        for (int b = 0; b < 8 && carry; ++b) { uint32_t t = cnt[b] & carry; cnt[b] ^= carry; carry = t; }
+        carry = nonzero & neg;
+        for (int b = 0; b < 8 && carry; ++b) { uint32_t t = cntm[b] & carry; cntm[b] ^= carry; carry = t; }
+    }
+}
