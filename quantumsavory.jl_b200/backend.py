@@ -1,0 +1,433 @@
+"""CudaBatchRepr / CudaBatchState: the backend generics of QuantumSavory on batched CUDA states.
+
+One `CudaBatchState` stands where the reference keeps one native state (`StateRef.state[]`,
+/root/reference/src/states_registers.jl:3-10) but carries N Monte-Carlo trajectories advanced in
+lockstep.  Method <-> reference generic (all reached only through the register layer, registers.py):
+
+    newstate(repr)                    newstate(::Qubit, repr)           quantumoptics.jl:66-72, clifford.jl:10-13
+    express(spec, repr)               express(state, repr)              src/baseops/initialize.jl:49
+    state.copy()                      Base.copy                          states_registers.jl:10
+    state.nsubsystems                 nsubsystems(state)
+    subsystemcompose(*states)         subsystemcompose(states...)       quantumoptics.jl:3-6, clifford.jl:1
+    state.apply(indices, op, mask)    apply!(state, indices, op)        src/representations.jl:4-7
+    state.uptotime(idx, bg, dt)       uptotime!(state, idx, bg, dt)     quantumoptics/uptotime.jl, clifford/uptotime.jl
+    state.observable(indices, obs)    observable(state, indices, obs)   quantumoptics.jl:14-45, clifford/express.jl:16-52
+    state.project_traceout(idx, b)    project_traceout!(state, idx, b)  quantumoptics.jl:47-64, clifford/express.jl:2-14
+    state.traceout(idx)               _traceout_state(state, idx)       src/baseops/traceout.jl:46, clifford.jl:7-8
+
+Indices are 1-BASED here, like the reference's `stateindex`; the C-ABI is 0-based.
+Measurement results are `BatchOutcome`s: `outcome == 2` is a per-trajectory mask that conditional
+`apply`/`traceout` calls consume (the "per-trajectory masks" of BASELINE.json's north_star).  With
+ntraj == 1 they convert to the plain `Int` the reference returns.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib, ops
+from . import symbols as S
+from ._lib import DM, KET, MCKET, TAB, check
+
+
+class BatchContext:
+    """One trajectory shard on one GPU (qsb_ctx).  Owns the per-call draw numbering."""
+
+    def __init__(self, ntraj: int, seed: int = 0x5153, device: int = 0, traj_offset: int = 0, stream: int | None = None):
+        self.L = _lib.lib()
+        p = C.c_void_p()
+        check(self.L.qsb_ctx_create(device, ntraj, traj_offset, seed, C.c_void_p(stream) if stream else None, C.byref(p)))
+        self.p = p
+        self.ntraj = ntraj
+        self.seed = seed
+        self.traj_offset = traj_offset
+        self.device = device
+        self._draw = 0
+
+    def next_draw(self) -> int:
+        d = self._draw
+        self._draw += 1
+        return d
+
+    def sync(self):
+        check(self.L.qsb_ctx_sync(self.p))
+
+    def counters(self):
+        c = (C.c_uint64 * 4)()
+        check(self.L.qsb_ctx_counters(self.p, c))
+        return {"launches": c[0], "algo_bytes": c[1], "ops": c[2], "draws": c[3]}
+
+    def reset_counters(self):
+        check(self.L.qsb_ctx_reset_counters(self.p))
+
+    def close(self):
+        if self.p:
+            self.L.qsb_ctx_destroy(self.p)
+            self.p = None
+
+    def mask(self, fill: bool) -> "BatchMask":
+        p = C.c_void_p()
+        check(self.L.qsb_mask_create(self.p, int(fill), C.byref(p)))
+        return BatchMask(self, p)
+
+    def random_mask(self, prob: float) -> "BatchMask":
+        p = C.c_void_p()
+        check(self.L.qsb_mask_random(self.p, float(prob), self.next_draw(), C.byref(p)))
+        return BatchMask(self, p)
+
+
+class BatchMask:
+    """One bit per trajectory."""
+
+    def __init__(self, ctx: BatchContext, p):
+        self.ctx, self.p = ctx, p
+
+    def __del__(self):
+        try:
+            if self.p and self.ctx.p:
+                self.ctx.L.qsb_mask_free(self.p)
+        except Exception:
+            pass
+        self.p = None
+
+    def _logic(self, other, op):
+        out = self.ctx.mask(False)
+        check(self.ctx.L.qsb_mask_logic(out.p, self.p, other.p if other is not None else None, op))
+        return out
+
+    def __and__(self, o): return self._logic(o, _lib.MASK_AND)
+    def __or__(self, o): return self._logic(o, _lib.MASK_OR)
+    def __xor__(self, o): return self._logic(o, _lib.MASK_XOR)
+    def __invert__(self): return self._logic(None, _lib.MASK_NOT)
+    def andnot(self, o): return self._logic(o, _lib.MASK_ANDNOT)
+
+    def count(self) -> int:
+        n = C.c_int64()
+        check(self.ctx.L.qsb_mask_count(self.p, C.byref(n)))
+        return n.value
+
+    def numpy(self) -> np.ndarray:
+        nw = (self.ctx.ntraj + 31) // 32
+        w = np.zeros(nw, np.uint32)
+        check(self.ctx.L.qsb_mask_to_host(self.p, w.ctypes.data_as(C.POINTER(C.c_uint32))))
+        bits = np.unpackbits(w.view(np.uint8), bitorder="little")[: self.ctx.ntraj]
+        return bits.astype(bool)
+
+    def __bool__(self):
+        if self.ctx.ntraj != 1:
+            raise TypeError("a BatchMask over more than one trajectory has no single truth value; pass it as mask=")
+        return bool(self.count())
+
+
+class BatchOutcome:
+    """Result of project_traceout! for all trajectories: 1-based outcomes in {1, 2}."""
+
+    def __init__(self, ctx, is2: BatchMask, alive: BatchMask, was_random: BatchMask | None = None):
+        self.ctx, self.is2, self.alive, self.was_random = ctx, is2, alive, was_random
+
+    def __eq__(self, other):
+        if isinstance(other, BatchOutcome):
+            return ~(self.is2 ^ other.is2) & (self.alive & other.alive)
+        if other == 2:
+            return self.is2
+        if other == 1:
+            return self.alive.andnot(self.is2)
+        return self.ctx.mask(False)
+
+    def __ne__(self, other):
+        if isinstance(other, BatchOutcome):
+            return (self.is2 ^ other.is2) & (self.alive & other.alive)
+        return self.alive.andnot(self == other)
+
+    __hash__ = None
+
+    def __int__(self):
+        if self.ctx.ntraj != 1:
+            raise TypeError("a BatchOutcome over more than one trajectory is not a single Int")
+        return 2 if self.is2.count() else 1
+
+    __index__ = __int__
+
+    def numpy(self) -> np.ndarray:
+        return 1 + self.is2.numpy().astype(np.int64)
+
+    def counts(self):
+        n2 = self.is2.count()
+        na = self.alive.count()
+        return {"alive": na, 1: na - n2, 2: n2}
+
+
+class BatchValue:
+    """observable() over all trajectories: ensemble statistics (+ per-trajectory values on request)."""
+
+    def __init__(self, ctx, stats, per_traj=None):
+        self.ctx = ctx
+        self.n_alive, self.sum, self.sumsq, self.sum_im = (float(x) for x in stats)
+        self._per_traj = per_traj
+
+    @property
+    def mean(self):
+        return self.sum / self.n_alive if self.n_alive else float("nan")
+
+    @property
+    def mean_complex(self):
+        return complex(self.sum, self.sum_im) / self.n_alive if self.n_alive else complex("nan")
+
+    @property
+    def var(self):
+        return self.sumsq / self.n_alive - self.mean**2 if self.n_alive else float("nan")
+
+    def __float__(self):
+        return self.mean
+
+    def __complex__(self):
+        return self.mean_complex
+
+    def values(self) -> np.ndarray:
+        if self._per_traj is None:
+            raise ValueError("per-trajectory values were not requested")
+        return self._per_traj
+
+
+def _ri(a) -> np.ndarray:
+    return np.ascontiguousarray(np.asarray(a, dtype=np.complex128)).view(np.float64).reshape(-1)
+
+
+def _colmajor_ri(m) -> np.ndarray:
+    return _ri(np.asarray(m, dtype=np.complex128).T.copy())
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _idx0(indices):
+    return (C.c_int * len(indices))(*[int(i) - 1 for i in indices])
+
+
+class CudaBatchRepr:
+    """The representation object that selects this backend (`reprs` of `Register(traits, reprs, bgs)`,
+    states_registers.jl:32-52).  formalism: "qo" (QuantumOpticsRepr), "mc" (QuantumMCRepr), "clifford"."""
+
+    def __init__(self, ctx: BatchContext, formalism: str = "qo"):
+        if formalism not in ("qo", "mc", "clifford"):
+            raise ValueError(formalism)
+        self.ctx, self.formalism = ctx, formalism
+
+    def __eq__(self, o):
+        return isinstance(o, CudaBatchRepr) and o.ctx is self.ctx and o.formalism == self.formalism
+
+    def __hash__(self):
+        return hash((id(self.ctx), self.formalism))
+
+    # newstate(::Qubit, repr)
+    def newstate(self):
+        kind = {"qo": KET, "mc": MCKET, "clifford": TAB}[self.formalism]
+        p = C.c_void_p()
+        check(self.ctx.L.qsb_state_new(self.ctx.p, kind, 1, C.byref(p)))
+        return CudaBatchState(self.ctx, p)
+
+    # express(state, repr): lower a host-side state description to a native batched state
+    def express(self, spec):
+        ctx = self.ctx
+        if isinstance(spec, CudaBatchState):
+            return spec
+        if self.formalism == "clifford":
+            if isinstance(spec, ops.StabilizerState) or isinstance(spec, ops.MixedStabilizer):
+                return CudaBatchState.from_generators(ctx, spec.n, spec.xs, spec.zs, spec.signs)
+            if isinstance(spec, ops.Mixture):
+                terms = [self.express(s) for _, s in spec.terms]
+                w = np.array([w for w, _ in spec.terms], dtype=np.float64)
+                arr = (C.c_void_p * len(terms))(*[t.p for t in terms])
+                p = C.c_void_p()
+                check(ctx.L.qsb_state_select(ctx.p, arr, _dp(w), len(terms), ctx.next_draw(), C.byref(p)))
+                return CudaBatchState(ctx, p)
+            raise _lib.MethodError(_lib.QSB_ERR_UNSUPPORTED, f"express({type(spec).__name__}, CliffordRepr) is not defined")
+        ketkind = KET if self.formalism == "qo" else MCKET
+        if isinstance(spec, ops.StabilizerState):
+            return CudaBatchState.from_array(ctx, spec.ket, ketkind)
+        if isinstance(spec, (ops.Mixture, ops.MixedStabilizer)):
+            return CudaBatchState.from_array(ctx, spec.dm, DM)
+        a = np.asarray(spec, dtype=np.complex128)
+        return CudaBatchState.from_array(ctx, a, ketkind if a.ndim == 1 else DM)
+
+
+class CudaBatchState:
+    """Opaque handle to N trajectories' copies of one native state (qsb_state)."""
+
+    ispadded = False  # ispadded(state) = false: removal physically drops the subsystem (traceout.jl:1-22)
+
+    def __init__(self, ctx: BatchContext, p):
+        self.ctx, self.p = ctx, p
+
+    def __del__(self):
+        try:
+            if self.p and self.ctx.p:
+                self.ctx.L.qsb_state_free(self.p)
+        except Exception:
+            pass
+        self.p = None
+
+    # -- construction ----------------------------------------------------------------------------
+    @classmethod
+    def from_array(cls, ctx, a, kind):
+        a = np.asarray(a, dtype=np.complex128)
+        n = int(round(np.log2(a.shape[0])))
+        data = _ri(a) if a.ndim == 1 else _colmajor_ri(a)
+        p = C.c_void_p()
+        check(ctx.L.qsb_state_from_host(ctx.p, kind, n, _dp(data), C.byref(p)))
+        return cls(ctx, p)
+
+    @classmethod
+    def from_generators(cls, ctx, n, xs, zs, signs):
+        xs = np.ascontiguousarray(xs, dtype=np.uint8); zs = np.ascontiguousarray(zs, dtype=np.uint8)
+        signs = np.ascontiguousarray(signs, dtype=np.uint8)
+        u8 = lambda a: a.ctypes.data_as(C.POINTER(C.c_uint8))
+        p = C.c_void_p()
+        check(ctx.L.qsb_tab_from_host(ctx.p, int(n), int(xs.shape[0]), u8(xs), u8(zs), u8(signs), C.byref(p)))
+        return cls(ctx, p)
+
+    @classmethod
+    def zeros(cls, ctx, kind, n):
+        p = C.c_void_p()
+        check(ctx.L.qsb_state_new(ctx.p, kind, n, C.byref(p)))
+        return cls(ctx, p)
+
+    # -- trait queries -----------------------------------------------------------------------------
+    @property
+    def kind(self):
+        return self.ctx.L.qsb_state_kind(self.p)
+
+    @property
+    def nsubsystems(self):
+        return self.ctx.L.qsb_state_nsubsystems(self.p)
+
+    @property
+    def default_repr(self):
+        return CudaBatchRepr(self.ctx, {KET: "qo", DM: "qo", MCKET: "mc", TAB: "clifford"}[self.kind])
+
+    def copy(self):
+        p = C.c_void_p()
+        check(self.ctx.L.qsb_state_copy(self.p, C.byref(p)))
+        return CudaBatchState(self.ctx, p)
+
+    def alive(self) -> BatchMask:
+        p = C.c_void_p()
+        check(self.ctx.L.qsb_state_alive(self.p, C.byref(p)))
+        return BatchMask(self.ctx, p)
+
+    def kill(self, lanes: BatchMask):
+        """Masked whole-group traceout!: the state stops existing on `lanes` only."""
+        check(self.ctx.L.qsb_state_kill(self.p, lanes.p))
+        return self
+
+    # -- read-back (tests) -------------------------------------------------------------------------
+    def trajectory(self, t: int) -> np.ndarray:
+        n, kind = self.nsubsystems, self.kind
+        L = 2**n if kind in (KET, MCKET) else 4**n
+        out = np.empty(2 * L)
+        check(self.ctx.L.qsb_state_to_host(self.p, t, _dp(out)))
+        v = out.view(np.complex128)
+        return v.copy() if kind in (KET, MCKET) else v.reshape(2**n, 2**n).T.copy()
+
+    def tableau(self, t: int):
+        n = self.nsubsystems
+        xs = np.zeros((2 * n, n), np.uint8); zs = np.zeros_like(xs); sg = np.zeros(2 * n, np.uint8); ac = np.zeros(n, np.uint8)
+        u8 = lambda a: a.ctypes.data_as(C.POINTER(C.c_uint8))
+        check(self.ctx.L.qsb_tab_to_host(self.p, t, u8(xs), u8(zs), u8(sg), u8(ac)))
+        return xs, zs, sg, ac
+
+    # -- backend generics ----------------------------------------------------------------------------
+    def subsystemcompose(self, *others):
+        states = (self,) + others
+        arr = (C.c_void_p * len(states))(*[s.p for s in states])
+        p = C.c_void_p()
+        check(self.ctx.L.qsb_tensor(self.ctx.p, arr, len(states), C.byref(p)))
+        return CudaBatchState(self.ctx, p)
+
+    def apply(self, indices, op, mask: BatchMask | None = None):
+        m = mask.p if mask is not None else None
+        if self.kind == TAB:
+            if not isinstance(op, ops.Gate):
+                raise _lib.MethodError(_lib.QSB_ERR_UNSUPPORTED, "apply! of a dense operator on a Clifford state")
+            try:
+                table = op.table
+            except ValueError as e:
+                raise _lib.MethodError(_lib.QSB_ERR_UNSUPPORTED, str(e))
+            check(self.ctx.L.qsb_apply_clifford(self.p, _idx0(indices), len(indices), table.ctypes.data_as(C.POINTER(C.c_uint8)), m))
+        else:
+            mat = op.mat if isinstance(op, ops.Gate) else np.asarray(op, dtype=np.complex128)
+            if mat.shape[0] != 2 ** len(indices):
+                raise _lib.ArgumentError(_lib.QSB_ERR_BAD_ARG, "operator size does not match the number of indices")
+            check(self.ctx.L.qsb_apply(self.p, _idx0(indices), len(indices), _dp(_colmajor_ri(mat)), m))
+        return self
+
+    def uptotime(self, idx, background, dt):
+        prm = (C.c_double * 2)(*background.params)
+        check(self.ctx.L.qsb_channel(self.p, int(idx) - 1, background.kind, prm, float(dt), self.ctx.next_draw()))
+        return self
+
+    def project_traceout(self, idx, basis):
+        """-> (BatchOutcome, self or None).  basis: ops.X/Y/Z (sigma^x..) or a pair of kets."""
+        ctx = self.ctx
+        alive = self.alive()
+        o, r = C.c_void_p(), C.c_void_p()
+        if isinstance(basis, ops.Gate) and basis.pauli in ("X", "Y", "Z"):
+            code, kets = {"X": 1, "Y": 2, "Z": 3}[basis.pauli], None
+        else:
+            code = _lib.BASIS_KETS
+            kets = _dp(_ri(np.stack([np.asarray(b, dtype=np.complex128) for b in basis])))
+        want_r = self.kind == TAB
+        check(ctx.L.qsb_measure(self.p, int(idx) - 1, code, kets, ctx.next_draw(), C.byref(o), C.byref(r) if want_r else None, None))
+        out = BatchOutcome(ctx, BatchMask(ctx, o), alive, BatchMask(ctx, r) if want_r and r else None)
+        return out, (self if self.nsubsystems > 0 else None)
+
+    def traceout(self, idx):
+        check(self.ctx.L.qsb_ptrace(self.p, int(idx) - 1, self.ctx.next_draw() if self.kind == MCKET else 0))
+        return self
+
+    def observable(self, indices, obs, per_trajectory: bool = False, stats_dev: int | None = None, sync: bool = True):
+        """-> BatchValue.  stats_dev: optional device pointer (double[4]) that receives the statistics
+        without a host sync (sync=False), e.g. a torch tensor that is NCCL-all-reduced later."""
+        ctx = self.ctx
+        k = len(indices)
+        sign = 0
+        keep = None
+        if isinstance(obs, ops.Gate) and obs.pauli is not None:
+            codes = np.array([{"I": 0, "X": 1, "Y": 2, "Z": 3}[c] for c in obs.pauli], np.uint8)
+            kind, ptr, keep = _lib.OBS_PAULI, codes.ctypes.data_as(C.c_void_p), codes
+        elif isinstance(obs, ops.SProjector):
+            if self.kind == TAB:
+                st = obs.state
+                if not isinstance(st, ops.StabilizerState):
+                    raise _lib.MethodError(_lib.QSB_ERR_UNSUPPORTED, "projector on a non-stabilizer ket for a Clifford state")
+                buf = np.concatenate([st.xs.reshape(-1), st.zs.reshape(-1), st.signs.reshape(-1)]).astype(np.uint8)
+                kind, ptr, keep = _lib.OBS_PROJ_STAB, buf.ctypes.data_as(C.c_void_p), buf
+            else:
+                buf = _ri(obs.ket)
+                kind, ptr, keep = _lib.OBS_PROJ_KET, buf.ctypes.data_as(C.c_void_p), buf
+        else:
+            mat = obs.mat if isinstance(obs, ops.Gate) else np.asarray(obs, dtype=np.complex128)
+            buf = _colmajor_ri(mat)
+            kind, ptr, keep = _lib.OBS_OP, buf.ctypes.data_as(C.c_void_p), buf
+        per_dev = None
+        per_t = None
+        if per_trajectory:
+            import torch
+            npad = (ctx.ntraj + 31) // 32 * 32
+            per_t = torch.empty(2 * npad, dtype=torch.float64, device=f"cuda:{ctx.device}")
+            per_dev = C.c_void_p(per_t.data_ptr())
+        stats = np.zeros(4)
+        check(ctx.L.qsb_expect(self.p, _idx0(indices), k, kind, ptr, sign, per_dev,
+                               C.c_void_p(stats_dev) if stats_dev else None, _dp(stats) if sync else None))
+        del keep
+        vals = None
+        if per_trajectory:
+            ctx.sync()
+            vals = per_t.cpu().numpy().view(np.complex128)[: ctx.ntraj]
+        return BatchValue(ctx, stats, vals)
+
+
+def subsystemcompose(*states):
+    return states[0].subsystemcompose(*states[1:])
