@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py -- trajectories/sec of the register-state hot path on B200 (contract in DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME] [--ntraj M]
+
+One "step" = one complete pass of the workload's event schedule over one lockstep ensemble of
+`ntraj` trajectories per GPU (weak scaling: every GPU owns its own block of global trajectory ids).
+Default workload = BASELINE.json configs[1]: firstgenrepeater, CliffordRepr tableaux, depolarizing
+noise, 10^6 trajectories per GPU.  Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+SEED = 0x5153
+FGR = dict(sizes=(2, 3, 4, 3, 2), F=0.97, t_end=25.0, dt_sample=0.2)  # 6.1_compare_formalisms_noplot.jl:11-21
+
+
+# ------------------------------------------------------------------------------------------------
+# workloads (shared by the GPU arm and the CPU arm: the same host code drives either backend)
+# ------------------------------------------------------------------------------------------------
+def wl_fgr(make_repr, formalism, record):
+    from qsb200 import symbols as S
+    from qsb200.workloads import firstgenrepeater as fgr
+    bg = S.Depolarization(100.0) if formalism == "clifford" else S.T1T2Noise(1000.0, 100.0)
+    _, _, net = fgr.monte_carlo_trajectory(make_repr, background=bg, record=record, **FGR)
+    return net.log
+
+
+def wl_sweep12(make_repr, formalism, record, n=12, rounds=2, seed=11):
+    """BASELINE.json configs[4]: composed n-qubit dm register; random 1q/2q gates, T1T2 noise on every
+    qubit, project_traceout! of the last qubit, re-compose a fresh |0>."""
+    from qsb200 import ops
+    from qsb200 import symbols as S
+    from qsb200.registers import Register, apply, initialize, observable, project_traceout, uptotime
+    rng = np.random.default_rng(seed)
+    reg = Register(n, make_repr(), S.T1T2Noise(100.0, 10.0))
+    for i in range(1, n, 2):
+        initialize((reg[i], reg[i + 1]), ops.DepolarizedBellPair(F=0.95))
+    for i in range(1, n - 1, 2):
+        apply((reg[i], reg[i + 2]), ops.CNOT)
+    t = 0.0
+    for r in range(rounds):
+        for _ in range(3):
+            apply(reg[int(rng.integers(n)) + 1], [ops.H, ops.X, ops.Z][rng.integers(3)])
+            a, b = (int(x) + 1 for x in rng.choice(n, 2, replace=False))
+            apply((reg[a], reg[b]), ops.CNOT)
+        t += float(rng.uniform(0.01, 0.1))
+        uptotime(reg[1:n], t)
+        m = project_traceout(reg[n], ops.Z)
+        initialize(reg[n], time=t)
+        apply((reg[n - 1], reg[n]), ops.CNOT)
+        record("ZZ", t, observable((reg[1], reg[2]), ops.tensor(ops.Z, ops.Z)))
+    return {"rounds": rounds, "n": n}
+
+
+WORKLOADS = {
+    "firstgenrepeater_clifford": dict(fn=wl_fgr, formalism="clifford", ntraj=1_000_000,
+                                      desc="examples/firstgenrepeater_lowlevel, sizes [2,3,4,3,2], F=0.97, CliffordRepr, Depolarization(100), t=0:0.2:25"),
+    "firstgenrepeater_dm": dict(fn=wl_fgr, formalism="qo", ntraj=1_000_000,
+                                desc="examples/firstgenrepeater_lowlevel, sizes [2,3,4,3,2], F=0.97, QuantumOpticsRepr dm, T1T2Noise(1000,100), t=0:0.2:25"),
+    "sweep12_dm": dict(fn=wl_sweep12, formalism="qo", ntraj=256,
+                       desc="12-qubit composed dm register: random H/X/Z + CNOT, T1T2Noise(100,10) on every qubit, project_traceout!, recompose"),
+}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's CPU path, one trajectory at a time on the host cores
+# ------------------------------------------------------------------------------------------------
+def _cpu_worker(args):
+    workload, traj_lo, traj_hi = args
+    sys.path.insert(0, ROOT)
+    import qsb200  # noqa: F401
+    from tests.oracle_backend import OracleContext, OracleRepr
+    w = WORKLOADS[workload]
+    acc = {}
+    t0 = time.perf_counter()
+    for t in range(traj_lo, traj_hi):
+        ctx = OracleContext(SEED, t)
+
+        def record(kind, tm, val, acc=acc):
+            a = acc.setdefault((kind, round(tm, 9)), [0, 0.0])
+            a[0] += 1; a[1] += float(np.real(complex(val)))
+        w["fn"](lambda: OracleRepr(ctx, w["formalism"]), w["formalism"], record)
+    return traj_hi - traj_lo, time.perf_counter() - t0, acc
+
+
+def cpu_run(workload, per_core, cores=None):
+    """Times `per_core` trajectories on each host core (processes, not threads: the driver is Python)."""
+    import multiprocessing as mp
+    cores = cores or os.cpu_count() or 1
+    jobs = [(workload, c * per_core, (c + 1) * per_core) for c in range(cores)]
+    t0 = time.perf_counter()
+    with mp.get_context("fork").Pool(cores) as pool:
+        res = pool.map(_cpu_worker, jobs)
+    wall = time.perf_counter() - t0
+    ntraj = sum(r[0] for r in res)
+    acc = {}
+    for r in res:
+        for k, (c, s) in r[2].items():
+            a = acc.setdefault(k, [0, 0.0]); a[0] += c; a[1] += s
+    return dict(ntraj=ntraj, wall=wall, cores=cores, stats=acc, busy=max(r[1] for r in res))
+
+
+def cpu_sample_size(workload):
+    return {"firstgenrepeater_clifford": 60, "firstgenrepeater_dm": 100, "sweep12_dm": 0}.get(workload, 20)
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        pw = [float(r[2]) for r in self.rows if len(r) >= 7 and r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm)}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class GpuRun:
+    """One workload on this rank's GPU: lockstep ensemble behind the C-ABI, statistics kept on the device."""
+
+    def __init__(self, workload, ntraj, rank, world, local_rank):
+        import torch
+        import qsb200  # noqa: F401
+        from qsb200.backend import BatchContext, CudaBatchRepr
+        from qsb200.sharding import StatsBuffer
+        self.torch = torch
+        self.w = WORKLOADS[workload]
+        self.ntraj, self.rank, self.world = ntraj, rank, world
+        torch.cuda.set_device(local_rank)
+        self.device = torch.device("cuda", local_rank)
+        self.stream = torch.cuda.Stream(device=self.device)
+        self.ctx = BatchContext(ntraj, seed=SEED, device=local_rank, traj_offset=rank * ntraj, stream=self.stream.cuda_stream)
+        self.CudaBatchRepr = CudaBatchRepr
+        self.stats = StatsBuffer(1024, self.device)
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.device)  # > 126 MB L2
+        self.h2d_bytes = 0
+
+    def step(self):
+        """One pass of the workload; returns (#observables recorded, host log).  No host sync inside."""
+        ctx, stats = self.ctx, self.stats
+        ctx._draw = 0
+        slot = [0]
+        keys = []
+
+        def record(kind, tm, val):
+            keys.append((kind, tm, None if hasattr(val, "n_alive") else val))
+
+        def make_repr():
+            return self.CudaBatchRepr(ctx, self.w["formalism"])
+
+        # observable(...) is asked to leave its statistics on the device (no sync): patch through kwargs
+        from qsb200 import registers
+        orig = registers.observable
+
+        def observable_nosync(refs, obs, something=None, time=None, **kw):
+            i = slot[0]
+            r = orig(refs, obs, something=something, time=time, stats_dev=stats.slot_ptr(i), sync=False)
+            if hasattr(r, "n_alive"):
+                slot[0] += 1
+            return r
+        registers.observable = observable_nosync
+        mods = [m for m in sys.modules.values() if getattr(m, "observable", None) is orig]
+        for m in mods:
+            m.observable = observable_nosync
+        try:
+            with self.torch.cuda.stream(self.stream):
+                log = self.w["fn"](make_repr, self.w["formalism"], record)
+        finally:
+            registers.observable = orig
+            for m in mods:
+                m.observable = orig
+        self.nobs = slot[0]
+        self.keys = keys
+        return log
+
+    def finish_step(self):
+        """The step's result crosses GPUs (one all-reduce) and comes back to the host (D2H)."""
+        with self.torch.cuda.stream(self.stream):
+            self.stats.allreduce()
+            host = self.stats.t[: max(self.nobs, 1)].cpu()
+        return host.numpy()
+
+
+def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, profile=True):
+    import torch
+    import torch.distributed as dist
+    g = GpuRun(workload, ntraj, rank, world, local_rank)
+    ctx = g.ctx
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        g.step(); g.finish_step()
+    barrier()
+    ctx.reset_counters()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dev_ms = 0.0
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        with torch.cuda.stream(g.stream):
+            g.flush.zero_()                       # flush L2 between timed iterations (not timed on the device clock)
+            ev0.record(g.stream)
+        log = g.step()
+        with torch.cuda.stream(g.stream):
+            ev1.record(g.stream)
+        host_stats = g.finish_step()              # e2e: all-reduce + D2H of the step's result
+        g.stream.synchronize()
+        dev_ms += ev0.elapsed_time(ev1)
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    counters = ctx.counters()
+    t = torch.tensor([dev_ms, wall * 1e3], dtype=torch.float64, device=g.device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms = float(t[0]), float(t[1])
+    out = dict(workload=workload, ntraj_per_gpu=ntraj, dev_ms_per_step=dev_ms / steps, wall_ms_per_step=wall_ms / steps,
+               value=ntraj * world * steps / (dev_ms / 1e3), e2e=ntraj * world * steps / (wall_ms / 1e3),
+               launches_per_step=counters["launches"] / steps, algo_bytes_per_step=counters["algo_bytes"] / steps,
+               ops_per_step=counters["ops"] / steps, nobs=g.nobs, d2h_bytes=g.nobs * 32, clocks=clocks, log=log,
+               sample_stats=host_stats[: min(4, len(host_stats))].tolist())
+    if profile and rank == 0:
+        ctx.profile(True)
+        g.step(); g.finish_step()
+        rows = ctx.profile_report()
+        ctx.profile(False)
+        rows = [r for r in rows if r["launches"]]
+        total = sum(r["ms"] for r in rows) or 1.0
+        rows.sort(key=lambda r: -r["ms"])
+        peak, which = measured_peak()
+        for r in rows:
+            r["share"] = r["ms"] / total
+            r["gbs"] = r["algo_bytes"] / (r["ms"] * 1e-3) / 1e9 if r["ms"] > 0 else 0.0
+            r["us_per_launch"] = 1e3 * r["ms"] / r["launches"]
+        top = rows[0]
+        out["kernels"] = rows[:8]
+        out["roofline"] = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["gbs"], "peak": peak, "unit": "GB/s",
+                           "frac": top["gbs"] / peak, "traffic": None, "peak_source": which,
+                           "algo_bytes_per_launch": top["algo_bytes"] / top["launches"], "us_per_launch": top["us_per_launch"],
+                           "share_of_step": top["share"]}
+    ctx.close()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="firstgenrepeater_clifford", choices=sorted(WORKLOADS))
+    ap.add_argument("--ntraj", type=int, default=0, help="trajectories per GPU (default: the config's)")
+    ap.add_argument("--extras", default="firstgenrepeater_dm,sweep12_dm", help="extra workloads reported under 'extra' (N=1 only)")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    w = WORKLOADS[args.workload]
+    ntraj = args.ntraj or w["ntraj"]
+    config = {"workload": f"{args.workload}: {w['desc']}", "trajectories_per_gpu": ntraj, "seed": SEED,
+              "l2": "L2 flushed (256 MiB memset) between timed steps; per-step state footprint >> L2 for the dm workloads",
+              "ensemble": "lockstep, shared classical schedule, per-trajectory masks (DESIGN.md)"}
+
+    if args.impl == "reference":
+        # the reference's own CPU path (oracle port: Julia is absent, DESIGN.md "Oracle"), all host cores, rank 0 only
+        if rank != 0:
+            return
+        per_core = max(1, cpu_sample_size(args.workload) // 4)
+        vals = []
+        for _ in range(max(1, args.warmup > 0)):
+            cpu_run(args.workload, 2)
+        for _ in range(args.steps):
+            r = cpu_run(args.workload, per_core)
+            vals.append(r["ntraj"] / r["wall"])
+        v = float(np.median(vals))
+        sample = f"{per_core} trajectories per core x {r['cores']} cores per step, {args.steps} steps (median)"
+        print(json.dumps({"impl": "reference", "metric": "trajectories/sec", "value": v, "unit": "trajectories/s", "n_gpus": args.gpus,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * r["wall"], "higher_is_better": True,
+                          "scaling": "weak", "vs_baseline": None, "dtype": "u32 bit-sliced tableau" if w["formalism"] == "clifford" else "f64 complex",
+                          "data": "synthetic", "config": config,
+                          "cpu_baseline": {"value": v, "unit": "trajectories/s", "cores": r["cores"], "kind": "port", "sample": sample},
+                          "e2e": {"value": v, "unit": "trajectories/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    main_res = run_gpu_workload(args.workload, ntraj, args.steps, args.warmup, rank, world, local_rank)
+    extra = {}
+    if world == 1 and args.extras:
+        for name in [x for x in args.extras.split(",") if x and x != args.workload]:
+            try:
+                r = run_gpu_workload(name, WORKLOADS[name]["ntraj"], max(2, min(args.steps, 3)), 3, 0, 1, local_rank)
+                extra[name] = {k: r[k] for k in ("ntraj_per_gpu", "dev_ms_per_step", "value", "e2e", "launches_per_step", "algo_bytes_per_step", "ops_per_step", "roofline", "kernels") if k in r}
+                extra[name]["state_ops_per_sec"] = r["ops_per_step"] / (r["dev_ms_per_step"] * 1e-3)
+            except Exception as e:  # an extra must never take the headline down
+                extra[name] = {"error": repr(e)[:300]}
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu and cpu_sample_size(args.workload):
+        per_core = cpu_sample_size(args.workload)
+        r = cpu_run(args.workload, per_core)
+        cpu = {"value": r["ntraj"] / r["wall"], "unit": "trajectories/s", "cores": r["cores"], "kind": "port",
+               "sample": f"{per_core} full trajectories per core on {r['cores']} processes ({r['wall']:.1f} s wall): oracle port driven by the same host schedule code"}
+    if rank == 0:
+        line = {"metric": "trajectories/sec", "value": main_res["value"], "unit": "trajectories/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": main_res["dev_ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u32 bit-sliced tableau" if w["formalism"] == "clifford" else "f64 complex", "data": "synthetic",
+                "config": config, "clocks": main_res["clocks"],
+                "e2e": {"value": main_res["e2e"], "unit": "trajectories/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": main_res["d2h_bytes"],
+                        "note": "wall clock around the public API calls incl. the all-reduce + D2H of the step's statistics; inputs are host-side symbols/matrices passed by value through the C-ABI"},
+                "gpu_launches": int(main_res["launches_per_step"] * args.steps),
+                "state_ops_per_sec": main_res["ops_per_step"] * world / (main_res["dev_ms_per_step"] * 1e-3),
+                "roofline": main_res.get("roofline"), "kernels": main_res.get("kernels"), "cpu_baseline": cpu,
+                "workload_log": main_res["log"], "extra": extra}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -83,6 +83,10 @@ int64_t qsb_ctx_ntraj(const qsb_ctx* ctx);
 /* counters[0]=kernel launches, [1]=algorithmic bytes (SURVEY 8d table x trajectories), [2]=state ops x trajectories, [3]=draw ids consumed */
 int qsb_ctx_counters(const qsb_ctx* ctx, uint64_t counters[4]);
 int qsb_ctx_reset_counters(qsb_ctx* ctx);
+/* Measurement aid: when enabled every kernel launch is bracketed by CUDA events on the context's
+ * stream; the report is a JSON array of {kernel, launches, ms, algo_bytes} rows (host-visible). */
+int qsb_ctx_profile(qsb_ctx* ctx, int enable);
+int qsb_ctx_profile_report(qsb_ctx* ctx, char* buf, size_t buflen);
 
 /* ---- state lifetime --------------------------------------------------------------------------*/
 /* newstate(::Qubit, repr): |0> ket / MCKet / tableau of Z1 -- quantumoptics.jl:66-72, clifford.jl:10-13;

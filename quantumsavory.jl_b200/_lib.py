@@ -71,6 +71,8 @@ def _declare(L):
         "qsb_ctx_ntraj": (C.c_int64, [vp]),
         "qsb_ctx_counters": (C.c_int, [vp, u64p]),
         "qsb_ctx_reset_counters": (C.c_int, [vp]),
+        "qsb_ctx_profile": (C.c_int, [vp, C.c_int]),
+        "qsb_ctx_profile_report": (C.c_int, [vp, C.c_char_p, C.c_size_t]),
         "qsb_state_new": (C.c_int, [vp, C.c_int, C.c_int, vpp]),
         "qsb_state_from_host": (C.c_int, [vp, C.c_int, C.c_int, dp, vpp]),
         "qsb_tab_from_host": (C.c_int, [vp, C.c_int, C.c_int, u8p, u8p, u8p, vpp]),

@@ -58,6 +58,15 @@ class BatchContext:
         check(self.L.qsb_ctx_counters(self.p, c))
         return {"launches": c[0], "algo_bytes": c[1], "ops": c[2], "draws": c[3]}
 
+    def profile(self, enable: bool):
+        check(self.L.qsb_ctx_profile(self.p, int(enable)))
+
+    def profile_report(self):
+        import json
+        buf = C.create_string_buffer(1 << 16)
+        check(self.L.qsb_ctx_profile_report(self.p, buf, len(buf)))
+        return json.loads(buf.value.decode())
+
     def reset_counters(self):
         check(self.L.qsb_ctx_reset_counters(self.p))
 

@@ -16,6 +16,83 @@ extern "C" const char* qsb_last_error(void) { return g_err; }
 extern "C" int qsb_version(void) { return 100; }
 
 // ---------------------------------------------------------------------------------------------
+// per-kernel profile: CUDA events on the launching stream around every launch (bench.py's roofline)
+// ---------------------------------------------------------------------------------------------
+struct ProfRow { std::string name; uint64_t launches = 0, bytes = 0; double ms = 0; };
+struct qsb_prof {
+    std::vector<ProfRow> rows;
+    std::vector<cudaEvent_t> pool;
+    struct Pending { int row; cudaEvent_t a, b; };
+    std::vector<Pending> pending;
+    int cur_row = -1; cudaEvent_t cur_a = nullptr;
+    int row_of(const char* name) {
+        for (size_t i = 0; i < rows.size(); ++i) if (rows[i].name == name) return (int)i;
+        ProfRow r; r.name = name; rows.push_back(r); return (int)rows.size() - 1;
+    }
+    cudaEvent_t get() {
+        if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+        cudaEvent_t e; cudaEventCreate(&e); return e;
+    }
+    void drain() {
+        for (auto& p : pending) {
+            float ms = 0; cudaEventElapsedTime(&ms, p.a, p.b);
+            rows[p.row].ms += ms; rows[p.row].launches++;
+            pool.push_back(p.a); pool.push_back(p.b);
+        }
+        pending.clear();
+    }
+};
+void qsb_prof_pre(qsb_ctx* ctx, const char* kernel) {
+    qsb_prof* P = ctx->prof;
+    P->cur_row = P->row_of(kernel);
+    P->cur_a = P->get();
+    cudaEventRecord(P->cur_a, ctx->stream);
+}
+void qsb_prof_post(qsb_ctx* ctx) {
+    qsb_prof* P = ctx->prof;
+    if (P->cur_row < 0) return;
+    cudaEvent_t b = P->get();
+    cudaEventRecord(b, ctx->stream);
+    P->pending.push_back({P->cur_row, P->cur_a, b});
+    P->cur_row = -1;
+    if (P->pending.size() >= 4096) { cudaStreamSynchronize(ctx->stream); P->drain(); }
+}
+void qsb_account(qsb_ctx* ctx, const char* kernel, uint64_t bytes) {
+    ctx->algo_bytes += bytes;
+    if (ctx->prof) ctx->prof->rows[ctx->prof->row_of(kernel)].bytes += bytes;
+}
+extern "C" int qsb_ctx_profile(qsb_ctx* ctx, int enable) {
+    if (!ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "null context");
+    if (enable && !ctx->prof) ctx->prof = new qsb_prof();
+    if (!enable && ctx->prof) {
+        cudaStreamSynchronize(ctx->stream);
+        ctx->prof->drain();
+        for (auto e : ctx->prof->pool) cudaEventDestroy(e);
+        delete ctx->prof; ctx->prof = nullptr;
+    }
+    return QSB_OK;
+}
+extern "C" int qsb_ctx_profile_report(qsb_ctx* ctx, char* buf, size_t buflen) {
+    if (!ctx || !buf || buflen < 4) QSB_FAIL(QSB_ERR_BAD_ARG, "bad argument");
+    std::string s = "[";
+    if (ctx->prof) {
+        QSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->prof->drain();
+        bool first = true;
+        for (auto& r : ctx->prof->rows) {
+            char line[256];
+            snprintf(line, sizeof(line), "%s{\"kernel\":\"%s\",\"launches\":%llu,\"ms\":%.6f,\"algo_bytes\":%llu}", first ? "" : ",",
+                     r.name.c_str(), (unsigned long long)r.launches, r.ms, (unsigned long long)r.bytes);
+            s += line; first = false;
+        }
+    }
+    s += "]";
+    if (s.size() + 1 > buflen) QSB_FAIL(QSB_ERR_BAD_ARG, "report buffer too small (%zu needed)", s.size() + 1);
+    memcpy(buf, s.c_str(), s.size() + 1);
+    return QSB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // allocation
 // ---------------------------------------------------------------------------------------------
 int qsb_dev_alloc(qsb_ctx* ctx, void** p, size_t bytes) {
@@ -165,6 +242,7 @@ extern "C" int qsb_ctx_create(int device, int64_t ntraj, int64_t traj_offset, ui
     QSB_TRY(qsb_dev_alloc(ctx, (void**)&ctx->stats_tmp, 8 * sizeof(double)));
     QSB_TRY(qsb_dev_alloc(ctx, (void**)&ctx->counts_tmp, 8 * sizeof(long long)));
     QSB_CUDA(cudaMemsetAsync(ctx->dev_flags, 0, 4 * sizeof(int), ctx->stream));
+    QSB_PRE(ctx, "k_valid_init");
     k_valid_init<<<wgrid(ctx->nwords), 256, 0, ctx->stream>>>(ctx->valid, ctx->nwords, ctx->ntraj);
     QSB_LAUNCH_CHECK(ctx);
     *out = ctx;
@@ -181,6 +259,7 @@ extern "C" int qsb_ctx_destroy(qsb_ctx* ctx) {
     if (ctx->scratch) cudaFreeAsync(ctx->scratch, ctx->stream);
     if (ctx->obs_buf) cudaFreeAsync(ctx->obs_buf, ctx->stream);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->prof) qsb_ctx_profile(ctx, 0);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return QSB_OK;
@@ -223,6 +302,7 @@ extern "C" int qsb_mask_create(qsb_ctx* ctx, int fill, qsb_mask** out) {
     if (!ctx || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     qsb_mask* m;
     QSB_TRY(qsb_mask_alloc(ctx, &m));
+    QSB_PRE(ctx, "k_mask_fill");
     k_mask_fill<<<wgrid(ctx->nwords), 256, 0, ctx->stream>>>(m->w, ctx->valid, ctx->nwords, fill);
     QSB_LAUNCH_CHECK(ctx);
     *out = m;
@@ -237,6 +317,7 @@ extern "C" int qsb_mask_free(qsb_mask* m) {
 extern "C" int qsb_mask_logic(qsb_mask* dst, const qsb_mask* a, const qsb_mask* b, int op) {
     if (!dst || !a || (op != QSB_MASK_NOT && !b)) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_mask_logic: null operand");
     qsb_ctx* ctx = dst->ctx;
+    QSB_PRE(ctx, "k_mask_logic");
     k_mask_logic<<<wgrid(ctx->nwords), 256, 0, ctx->stream>>>(dst->w, a->w, b ? b->w : nullptr, ctx->valid, ctx->nwords, op);
     QSB_LAUNCH_CHECK(ctx);
     return QSB_OK;
@@ -246,6 +327,7 @@ extern "C" int qsb_mask_count(const qsb_mask* m, int64_t* out) {
     qsb_ctx* ctx = m->ctx;
     QSB_CUDA(cudaMemsetAsync(ctx->counts_tmp, 0, sizeof(long long), ctx->stream));
     unsigned g = wgrid(ctx->nwords); if (g > 1024) g = 1024;
+    QSB_PRE(ctx, "k_mask_count");
     k_mask_count<<<g, 256, 0, ctx->stream>>>(m->w, ctx->nwords, ctx->counts_tmp);
     QSB_LAUNCH_CHECK(ctx);
     long long h = 0;
@@ -264,6 +346,7 @@ extern "C" int qsb_mask_from_host(qsb_mask* m, const uint32_t* words) {
     if (!m || !words) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     qsb_ctx* ctx = m->ctx;
     QSB_CUDA(cudaMemcpyAsync(m->w, words, ctx->nwords * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    QSB_PRE(ctx, "k_mask_logic");
     k_mask_logic<<<wgrid(ctx->nwords), 256, 0, ctx->stream>>>(m->w, m->w, m->w, ctx->valid, ctx->nwords, QSB_MASK_AND);
     QSB_LAUNCH_CHECK(ctx);
     return QSB_OK;
@@ -272,6 +355,7 @@ extern "C" int qsb_mask_random(qsb_ctx* ctx, double p, uint64_t draw_id, qsb_mas
     if (!ctx || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     qsb_mask* m;
     QSB_TRY(qsb_mask_alloc(ctx, &m));
+    QSB_PRE(ctx, "k_mask_random");
     k_mask_random<<<(unsigned)((ctx->npad + 255) / 256), 256, 0, ctx->stream>>>(m->w, ctx->valid, ctx->npad, ctx->seed, (uint64_t)ctx->traj_offset, draw_id, p);
     QSB_LAUNCH_CHECK(ctx);
     ctx->draws++;
@@ -289,6 +373,7 @@ extern "C" int qsb_state_alive(const qsb_state* st, qsb_mask** out) {
 extern "C" int qsb_state_kill(qsb_state* st, const qsb_mask* lanes) {
     if (!st || !lanes) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     qsb_ctx* ctx = st->ctx;
+    QSB_PRE(ctx, "k_kill");
     k_kill<<<wgrid(ctx->nwords), 256, 0, ctx->stream>>>(st->alive, lanes->w, ctx->nwords);
     QSB_LAUNCH_CHECK(ctx);
     return QSB_OK;

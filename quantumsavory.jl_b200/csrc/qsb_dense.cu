@@ -43,6 +43,7 @@ __global__ void k_alive_and(uint32_t* out, const uint32_t* a, const uint32_t* b,
     if (w < nwords) out[w] = a[w] & b[w];
 }
 static int alive_init(qsb_ctx* ctx, qsb_state* st) {
+    QSB_PRE(ctx, "k_alive_init");
     k_alive_init<<<(unsigned)((ctx->nwords + 255) / 256), 256, 0, ctx->stream>>>(st->alive, ctx->valid, ctx->nwords);
     QSB_LAUNCH_CHECK(ctx);
     return QSB_OK;
@@ -67,6 +68,7 @@ int qsbd_new(qsb_ctx* ctx, int kind, int n, qsb_state** out) {
     QSB_TRY(qsb_state_alloc(ctx, kind, n, &st));
     size_t elems = st->bytes / (ctx->npad * sizeof(double2));
     Grid2 g = plan_grid(ctx, elems);
+    QSB_PRE(ctx, "k_fill0");
     k_fill0<<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, elems);
     QSB_LAUNCH_CHECK(ctx);
     QSB_TRY(alive_init(ctx, st));
@@ -80,10 +82,11 @@ int qsbd_from_host(qsb_ctx* ctx, int kind, int n, const double* data, qsb_state*
     void* src;
     QSB_TRY(qsb_upload(ctx, data, elems * sizeof(double2), &src));
     Grid2 g = plan_grid(ctx, elems);
+    QSB_PRE(ctx, "k_broadcast");
     k_broadcast<<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, (const double2*)src, ctx->npad, elems);
     QSB_LAUNCH_CHECK(ctx);
     QSB_TRY(alive_init(ctx, st));
-    ctx->algo_bytes += (uint64_t)elems * 16 * ctx->ntraj; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_broadcast", (uint64_t)elems * 16 * ctx->ntraj); ctx->ops += ctx->ntraj;
     *out = st;
     return QSB_OK;
 }
@@ -113,9 +116,10 @@ int qsbd_select(qsb_ctx* ctx, const qsb_state* const* states, const double* w, i
     for (int i = 0; i < m; ++i) total += w[i];
     for (int i = 0; i < m; ++i) { cum += w[i] / total; a.cum[i] = cum; a.src[i] = (const double2*)states[i]->data; a.alive[i] = states[i]->alive; }
     Grid2 g = plan_grid(ctx, elems);
+    QSB_PRE(ctx, "k_select");
     k_select<<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, st->alive, a, ctx->npad, elems, ctx->seed, (uint64_t)ctx->traj_offset, draw_id);
     QSB_LAUNCH_CHECK(ctx);
-    ctx->algo_bytes += (uint64_t)elems * 32 * ctx->ntraj; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_select", (uint64_t)elems * 32 * ctx->ntraj); ctx->ops += ctx->ntraj;
     *out = st;
     return QSB_OK;
 }
@@ -136,6 +140,7 @@ int qsbd_promote_dm(qsb_state* st) {
     void* nd;
     QSB_TRY(qsb_dev_alloc(ctx, &nd, nbytes));
     Grid2 g = plan_grid(ctx, (size_t)1 << (2 * st->n));
+    QSB_PRE(ctx, "k_outer");
     k_outer<<<g.grid, TPB, 0, ctx->stream>>>((double2*)nd, (const double2*)st->data, ctx->npad, st->n);
     QSB_LAUNCH_CHECK(ctx);
     QSB_TRY(qsb_dev_free(ctx, st->data));
@@ -186,15 +191,17 @@ int qsbd_tensor2(qsb_ctx* ctx, const qsb_state* a, const qsb_state* b, qsb_state
     QSB_TRY(qsb_state_alloc(ctx, kind, a->n + b->n, &st));
     size_t La = kind == QSB_DM ? (size_t)1 << (2 * a->n) : (size_t)1 << a->n;
     Grid2 g = plan_grid(ctx, La);
+    QSB_PRE(ctx, "k_tensor");
     if (kind == QSB_DM) k_tensor<true><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, (const double2*)xa->data, (const double2*)xb->data, ctx->npad, a->n, b->n);
     else k_tensor<false><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, (const double2*)xa->data, (const double2*)xb->data, ctx->npad, a->n, b->n);
     QSB_LAUNCH_CHECK(ctx);
+    QSB_PRE(ctx, "k_alive_and");
     k_alive_and<<<(unsigned)((ctx->nwords + 255) / 256), 256, 0, ctx->stream>>>(st->alive, a->alive, b->alive, ctx->nwords);
     QSB_LAUNCH_CHECK(ctx);
     if (pa) qsb_state_free(pa);
     if (pb) qsb_state_free(pb);
     size_t ea = xa->bytes / ctx->npad, eb = xb->bytes / ctx->npad, eo = st->bytes / ctx->npad;
-    ctx->algo_bytes += (uint64_t)(ea + eb + eo) * ctx->ntraj; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_tensor", (uint64_t)(ea + eb + eo) * ctx->ntraj); ctx->ops += ctx->ntraj;
     *out = st;
     return QSB_OK;
 }
@@ -304,17 +311,19 @@ int qsbd_apply(qsb_state* st, const int* idx, int k, const double* U, const qsb_
         sort_ints(a.sorted, k);
         size_t groups = (size_t)1 << (n - k);
         Grid2 g = plan_grid(ctx, groups);
+        QSB_PRE(ctx, "k_apply_ket");
         if (k == 1) k_apply_ket<1><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, a, mw);
         else k_apply_ket<2><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, a, mw);
-        ctx->algo_bytes += (uint64_t)32 * ((uint64_t)1 << n) * ctx->ntraj;
+        qsb_account(ctx, "k_apply_ket", (uint64_t)32 * ((uint64_t)1 << n) * ctx->ntraj);
     } else {
         for (int i = 0; i < k; ++i) { a.sorted[i] = idx[i]; a.sorted[k + i] = idx[i] + n; }
         sort_ints(a.sorted, 2 * k);
         size_t groups = (size_t)1 << (2 * n - 2 * k);
         Grid2 g = plan_grid(ctx, groups);
+        QSB_PRE(ctx, "k_apply_dm");
         if (k == 1) k_apply_dm<1><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, n, a, mw);
         else k_apply_dm<2><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, n, a, mw);
-        ctx->algo_bytes += (uint64_t)32 * ((uint64_t)1 << (2 * n)) * ctx->ntraj;
+        qsb_account(ctx, "k_apply_dm", (uint64_t)32 * ((uint64_t)1 << (2 * n)) * ctx->ntraj);
     }
     QSB_LAUNCH_CHECK(ctx);
     ctx->ops += ctx->ntraj;
@@ -384,6 +393,7 @@ static int launch_rdm1(qsb_state* st, int q, int* nsplit_out) {
     // layout: [partials nsplit*4*npad][scale npad][sel npad (as double-sized slots for alignment)]
     QSB_TRY(qsb_ensure_scratch(ctx, ((size_t)nsplit * 4 + 2) * ctx->npad * sizeof(double)));
     dim3 grid((unsigned)((ctx->npad + TPB - 1) / TPB), nsplit, 1);
+    QSB_PRE(ctx, "k_rdm1");
     if (st->kind == QSB_DM) k_rdm1<true><<<grid, TPB, 0, ctx->stream>>>((const double2*)st->data, ctx->npad, st->n, q, range, nsplit, ctx->scratch);
     else k_rdm1<false><<<grid, TPB, 0, ctx->stream>>>((const double2*)st->data, ctx->npad, st->n, q, range, nsplit, ctx->scratch);
     QSB_LAUNCH_CHECK(ctx);
@@ -478,13 +488,15 @@ int qsbd_channel(qsb_state* st, int idx, int bg, const double* prm, double dt, u
         QSB_TRY(launch_rdm1(st, idx, &nsplit));
         double* scale = ctx->scratch + (size_t)nsplit * 4 * ctx->npad;
         int* sel = (int*)(scale + ctx->npad);
+        QSB_PRE(ctx, "k_mc_finalize");
         k_mc_finalize<<<(unsigned)((ctx->npad + 255) / 256), 256, 0, ctx->stream>>>(ctx->scratch, nsplit, ctx->npad, ka, ctx->seed, (uint64_t)ctx->traj_offset, draw_id, scale, sel);
         QSB_LAUNCH_CHECK(ctx);
         size_t groups = (size_t)1 << (n - 1);
         Grid2 g = plan_grid(ctx, groups);
+        QSB_PRE(ctx, "k_apply_kraus_sel");
         k_apply_kraus_sel<<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, idx, ka, scale, sel);
         QSB_LAUNCH_CHECK(ctx);
-        ctx->algo_bytes += (uint64_t)32 * ((uint64_t)1 << n) * ctx->ntraj; ctx->ops += ctx->ntraj; ctx->draws++;
+        qsb_account(ctx, "k_apply_kraus_sel", (uint64_t)32 * ((uint64_t)1 << n) * ctx->ntraj); ctx->ops += ctx->ntraj; ctx->draws++;
         return QSB_OK;
     }
     if (st->kind == QSB_KET) QSB_TRY(qsbd_promote_dm(st));  // uptotime.jl:1-4
@@ -507,9 +519,10 @@ int qsbd_channel(qsb_state* st, int idx, int bg, const double* prm, double dt, u
     }
     size_t groups = (size_t)1 << (2 * n - 2);
     Grid2 g = plan_grid(ctx, groups);
+    QSB_PRE(ctx, "k_channel_dm");
     k_channel_dm<<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, p);
     QSB_LAUNCH_CHECK(ctx);
-    ctx->algo_bytes += (uint64_t)(p.offdiag_only ? 16 : 32) * ((uint64_t)1 << (2 * n)) * ctx->ntraj; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_channel_dm", (uint64_t)(p.offdiag_only ? 16 : 32) * ((uint64_t)1 << (2 * n)) * ctx->ntraj); ctx->ops += ctx->ntraj;
     return QSB_OK;
 }
 
@@ -604,6 +617,7 @@ int qsbd_measure(qsb_state* st, int idx, const double* kets, uint64_t draw_id, q
     double* scale = ctx->scratch + (size_t)nsplit * 4 * ctx->npad;
     int* sel = (int*)(scale + ctx->npad);
     if (counts_host) QSB_CUDA(cudaMemsetAsync(ctx->counts_tmp, 0, 3 * sizeof(long long), ctx->stream));
+    QSB_PRE(ctx, "k_measure_finalize");
     k_measure_finalize<<<(unsigned)((ctx->npad + 255) / 256), 256, 0, ctx->stream>>>(ctx->scratch, nsplit, ctx->npad, ma, ket ? 1 : 0, 1,
         ctx->seed, (uint64_t)ctx->traj_offset, draw_id, st->alive, scale, sel, outcome2->w, counts_host ? ctx->counts_tmp : nullptr, ctx->dev_flags);
     QSB_LAUNCH_CHECK(ctx);
@@ -619,13 +633,14 @@ int qsbd_measure(qsb_state* st, int idx, const double* kets, uint64_t draw_id, q
         QSB_TRY(qsb_dev_alloc(ctx, &nd, nbytes));
         size_t groups = ket ? (size_t)1 << (n - 1) : (size_t)1 << (2 * n - 2);
         Grid2 g = plan_grid(ctx, groups);
+        QSB_PRE(ctx, "k_project");
         if (ket) k_project<false><<<g.grid, TPB, 0, ctx->stream>>>((double2*)nd, (const double2*)st->data, ctx->npad, n, idx, groups, ma, scale, sel);
         else k_project<true><<<g.grid, TPB, 0, ctx->stream>>>((double2*)nd, (const double2*)st->data, ctx->npad, n, idx, groups, ma, scale, sel);
         QSB_LAUNCH_CHECK(ctx);
         QSB_TRY(qsb_dev_free(ctx, st->data));
         st->data = nd; st->bytes = nbytes; st->n = n - 1;
     }
-    ctx->algo_bytes += (uint64_t)16 * (elems_in + elems_in / (ket ? 2 : 4)) * ctx->ntraj; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_project", (uint64_t)16 * (elems_in + elems_in / (ket ? 2 : 4)) * ctx->ntraj); ctx->ops += ctx->ntraj;
     if (counts_host) QSB_TRY(fetch_counts(ctx, counts_host));
     return QSB_OK;
 }
@@ -672,11 +687,13 @@ int qsbd_ptrace(qsb_state* st, int idx, uint64_t draw_id) {
     size_t groups = (size_t)1 << (2 * n - 2);
     Grid2 g = plan_grid(ctx, groups);
     if (st->kind == QSB_DM) {
+        QSB_PRE(ctx, "k_ptrace_dm");
         k_ptrace_dm<<<g.grid, TPB, 0, ctx->stream>>>((double2*)nd, (const double2*)st->data, ctx->npad, n, idx, groups);
-        ctx->algo_bytes += (uint64_t)16 * (((uint64_t)1 << (2 * n)) / 2 + ((uint64_t)1 << (2 * n - 2))) * ctx->ntraj;
+        qsb_account(ctx, "k_ptrace_dm", (uint64_t)16 * (((uint64_t)1 << (2 * n)) / 2 + ((uint64_t)1 << (2 * n - 2))) * ctx->ntraj);
     } else {
+        QSB_PRE(ctx, "k_ptrace_ket");
         k_ptrace_ket<<<g.grid, TPB, 0, ctx->stream>>>((double2*)nd, (const double2*)st->data, ctx->npad, n, idx, groups);
-        ctx->algo_bytes += (uint64_t)16 * (((uint64_t)1 << n) + ((uint64_t)1 << (2 * n - 2))) * ctx->ntraj;
+        qsb_account(ctx, "k_ptrace_ket", (uint64_t)16 * (((uint64_t)1 << n) + ((uint64_t)1 << (2 * n - 2))) * ctx->ntraj);
     }
     QSB_LAUNCH_CHECK(ctx);
     QSB_TRY(qsb_dev_free(ctx, st->data));
@@ -866,17 +883,20 @@ int qsbd_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* 
     size_t need = ((size_t)nsplit * 2 * ctx->npad + (size_t)fblocks * 4) * sizeof(double);
     QSB_TRY(qsb_ensure_scratch(ctx, need));
     dim3 grid((unsigned)((ctx->npad + TPB - 1) / TPB), nsplit, 1);
+    QSB_PRE(ctx, "k_expect");
     k_expect<<<grid, TPB, 0, ctx->stream>>>((const double2*)st->data, ctx->npad, a, range, nsplit, ctx->scratch);
     QSB_LAUNCH_CHECK(ctx);
     double* blockstats = ctx->scratch + (size_t)nsplit * 2 * ctx->npad;
+    QSB_PRE(ctx, "k_expect_finalize");
     k_expect_finalize<<<fblocks, 256, 0, ctx->stream>>>(ctx->scratch, nsplit, ctx->npad, factor, square_abs, st->alive, per_traj, blockstats);
     QSB_LAUNCH_CHECK(ctx);
     double* sd = stats_dev ? stats_dev : ctx->stats_tmp;
     if (stats_dev || stats_host) {
+        QSB_PRE(ctx, "k_stats_final");
         k_stats_final<<<1, 256, 0, ctx->stream>>>(blockstats, (int)fblocks, sd);
         QSB_LAUNCH_CHECK(ctx);
     }
-    ctx->algo_bytes += algo * ctx->ntraj; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_expect", algo * ctx->ntraj); ctx->ops += ctx->ntraj;
     if (stats_host) {
         QSB_CUDA(cudaMemcpyAsync(stats_host, sd, 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
         QSB_TRY(qsb_ctx_sync(ctx));

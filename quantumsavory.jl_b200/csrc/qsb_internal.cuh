@@ -46,6 +46,7 @@ struct qsb_ctx {
     size_t host_stage_bytes;
     uint64_t launches, algo_bytes, ops, draws;
     int sm_count;
+    struct qsb_prof* prof;  // per-kernel CUDA-event timing, off unless qsb_ctx_profile(ctx, 1)
 };
 
 struct qsb_state {
@@ -69,8 +70,14 @@ void qsb_set_error(const char* fmt, ...);
     qsb_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
     return e_ == cudaErrorMemoryAllocation ? QSB_ERR_OOM : QSB_ERR_CUDA; } } while (0)
 #define QSB_TRY(expr) do { int rc_ = (expr); if (rc_ != QSB_OK) return rc_; } while (0)
-#define QSB_LAUNCH_CHECK(ctx) do { (ctx)->launches++; cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { \
+#define QSB_LAUNCH_CHECK(ctx) do { (ctx)->launches++; if ((ctx)->prof) qsb_prof_post(ctx); cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { \
     qsb_set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(e_), __FILE__, __LINE__); return QSB_ERR_CUDA; } } while (0)
+// brackets the next launch with CUDA events on the context's stream when profiling is on
+#define QSB_PRE(ctx, name) do { if ((ctx)->prof) qsb_prof_pre(ctx, name); } while (0)
+void qsb_prof_pre(qsb_ctx* ctx, const char* kernel);
+void qsb_prof_post(qsb_ctx* ctx);
+// adds an op's algorithmic bytes (SURVEY 8d table x trajectories) to the context total and to `kernel`'s row
+void qsb_account(qsb_ctx* ctx, const char* kernel, uint64_t bytes);
 
 // ---- allocation -------------------------------------------------------------------------------
 int qsb_dev_alloc(qsb_ctx* ctx, void** p, size_t bytes);

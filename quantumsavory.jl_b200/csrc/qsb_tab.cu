@@ -27,6 +27,7 @@ __global__ void k_tab_init(uint32_t* p, uint32_t* alive, const uint32_t* valid, 
 int qsbt_new(qsb_ctx* ctx, int n, int active, qsb_state** out) {
     qsb_state* st;
     QSB_TRY(qsb_state_alloc(ctx, QSB_TAB, n, &st));
+    QSB_PRE(ctx, "k_tab_init");
     k_tab_init<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, st->alive, ctx->valid, (size_t)ctx->nwords, n, active);
     QSB_LAUNCH_CHECK(ctx);
     *out = st;
@@ -44,10 +45,11 @@ int qsbt_tensor2(qsb_ctx* ctx, const qsb_state* a, const qsb_state* b, qsb_state
     if (a->n + b->n > MAXN) QSB_FAIL(QSB_ERR_UNSUPPORTED, "composite tableau would exceed %d qubits", MAXN);
     qsb_state* st;
     QSB_TRY(qsb_state_alloc(ctx, QSB_TAB, a->n + b->n, &st));
+    QSB_PRE(ctx, "k_tab_tensor");
     k_tab_tensor<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, st->alive, (const uint32_t*)a->data, (const uint32_t*)b->data, a->alive, b->alive,
                                                        (size_t)ctx->nwords, a->n, b->n);
     QSB_LAUNCH_CHECK(ctx);
-    ctx->algo_bytes += (uint64_t)(qsb_tab_planes(a->n) + qsb_tab_planes(b->n) + qsb_tab_planes(st->n)) * ctx->ntraj / 8; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_tab_tensor", (uint64_t)(qsb_tab_planes(a->n) + qsb_tab_planes(b->n) + qsb_tab_planes(st->n)) * ctx->ntraj / 8); ctx->ops += ctx->ntraj;
     *out = st;
     return QSB_OK;
 }
@@ -81,9 +83,10 @@ int qsbt_select(qsb_ctx* ctx, const qsb_state* const* states, const double* w, i
     double total = 0, cum = 0;
     for (int i = 0; i < m; ++i) total += w[i];
     for (int i = 0; i < m; ++i) { cum += w[i] / total; a.cum[i] = cum; a.src[i] = (const uint32_t*)states[i]->data; a.alive[i] = states[i]->alive; }
+    QSB_PRE(ctx, "k_tab_select");
     k_tab_select<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, st->alive, a, (size_t)ctx->nwords, qsb_tab_planes(st->n), ctx->seed, (uint64_t)ctx->traj_offset, draw_id);
     QSB_LAUNCH_CHECK(ctx);
-    ctx->algo_bytes += (uint64_t)2 * qsb_tab_planes(st->n) * ctx->ntraj / 8; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_tab_select", (uint64_t)2 * qsb_tab_planes(st->n) * ctx->ntraj / 8); ctx->ops += ctx->ntraj;
     *out = st;
     return QSB_OK;
 }
@@ -132,9 +135,10 @@ int qsbt_apply(qsb_state* st, const int* idx, int k, const uint8_t* table, const
     }
     if (table[0] != 0) QSB_FAIL(QSB_ERR_BAD_ARG, "conjugation table maps the identity to a non-identity");
     for (int b = 0; b < nb; ++b) for (int j = 0; j < nb; ++j) if ((cols[j] >> b) & 1) a.outmask[b] |= 1 << j;
+    QSB_PRE(ctx, "k_tab_gate");
     k_tab_gate<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (size_t)ctx->nwords, a, mask ? mask->w : nullptr);
     QSB_LAUNCH_CHECK(ctx);
-    ctx->algo_bytes += (uint64_t)2 * (2 * st->n) * (2 * k + 2) * ctx->ntraj / 8; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_tab_gate", (uint64_t)2 * (2 * st->n) * (2 * k + 2) * ctx->ntraj / 8); ctx->ops += ctx->ntraj;
     return QSB_OK;
 }
 
@@ -157,9 +161,10 @@ int qsbt_channel(qsb_state* st, int idx, int bg, const double* prm, double dt, u
     else QSB_FAIL(QSB_ERR_UNSUPPORTED, "no paulinoise method for this background on a Clifford state (reference raises MethodError)");
     double cum = 1.0;
     for (int i = 0; i < a.np; ++i) { cum -= probs[i]; a.cum[i] = cum; }
+    QSB_PRE(ctx, "k_tab_noise");
     k_tab_noise<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (size_t)ctx->nwords, a, ctx->seed, (uint64_t)ctx->traj_offset, draw_id);
     QSB_LAUNCH_CHECK(ctx);
-    ctx->algo_bytes += (uint64_t)(2 * st->n) * 3 * ctx->ntraj / 8; ctx->ops += ctx->ntraj; ctx->draws++;
+    qsb_account(ctx, "k_tab_noise", (uint64_t)(2 * st->n) * 3 * ctx->ntraj / 8); ctx->ops += ctx->ntraj; ctx->draws++;
     return QSB_OK;
 }
 
@@ -207,10 +212,11 @@ int qsbt_measure(qsb_state* st, int idx, int basis, uint64_t draw_id, qsb_mask* 
     void* nd;
     QSB_TRY(qsb_dev_alloc(ctx, &nd, qsb_state_bytes(ctx, QSB_TAB, n - 1)));
     if (counts_host) QSB_CUDA(cudaMemsetAsync(ctx->counts_tmp, 0, 3 * sizeof(long long), ctx->stream));
+    QSB_PRE(ctx, "k_tab_measure");
     k_tab_measure<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (uint32_t*)nd, (size_t)ctx->nwords, n, idx, tx, tz, ctx->seed, (uint64_t)ctx->traj_offset, draw_id,
                                                         st->alive, outcome2->w, was_random ? was_random->w : nullptr, counts_host ? ctx->counts_tmp : nullptr);
     QSB_LAUNCH_CHECK(ctx);
-    ctx->algo_bytes += (uint64_t)(qsb_tab_planes(n) + qsb_tab_planes(n - 1)) * ctx->ntraj / 8; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_tab_measure", (uint64_t)(qsb_tab_planes(n) + qsb_tab_planes(n - 1)) * ctx->ntraj / 8); ctx->ops += ctx->ntraj;
     QSB_TRY(swap_in(st, nd, n - 1));
     if (counts_host) {
         long long h[3];
@@ -225,9 +231,10 @@ int qsbt_ptrace(qsb_state* st, int idx) {
     int n = st->n;
     void* nd;
     QSB_TRY(qsb_dev_alloc(ctx, &nd, qsb_state_bytes(ctx, QSB_TAB, n - 1)));
+    QSB_PRE(ctx, "k_tab_ptrace");
     k_tab_ptrace<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (uint32_t*)nd, (size_t)ctx->nwords, n, idx);
     QSB_LAUNCH_CHECK(ctx);
-    ctx->algo_bytes += (uint64_t)(qsb_tab_planes(n) + qsb_tab_planes(n - 1)) * ctx->ntraj / 8; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_tab_ptrace", (uint64_t)(qsb_tab_planes(n) + qsb_tab_planes(n - 1)) * ctx->ntraj / 8); ctx->ops += ctx->ntraj;
     return swap_in(st, nd, n - 1);
 }
 int qsbt_from_host(qsb_ctx* ctx, int n, int ngen, const uint8_t* xs, const uint8_t* zs, const uint8_t* signs, qsb_state** out) {
@@ -243,10 +250,11 @@ int qsbt_from_host(qsb_ctx* ctx, int n, int ngen, const uint8_t* xs, const uint8
         uint32_t px = 0, pz = 0;
         for (int q = 0; q < n; ++q) { if (xs[g * n + q]) px |= 1u << q; if (zs[g * n + q]) pz |= 1u << q; }
         if ((px | pz) == 0) { qsb_state_free(st); QSB_FAIL(QSB_ERR_BAD_ARG, "stabilizer generator %d is the identity", g + 1); }
+        QSB_PRE(ctx, "k_tab_force");
         k_tab_force<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (size_t)ctx->nwords, n, px, pz, signs ? signs[g] : 0);
         QSB_LAUNCH_CHECK(ctx);
     }
-    ctx->algo_bytes += (uint64_t)qsb_tab_planes(n) * ctx->ntraj / 8; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_tab_force", (uint64_t)qsb_tab_planes(n) * ctx->ntraj / 8); ctx->ops += ctx->ntraj;
     *out = st;
     return QSB_OK;
 }
@@ -328,9 +336,10 @@ int qsbt_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* 
     }
     double* sd = stats_dev ? stats_dev : ((stats_host) ? ctx->stats_tmp : nullptr);
     if (sd) QSB_CUDA(cudaMemsetAsync(sd, 0, 4 * sizeof(double), ctx->stream));
+    QSB_PRE(ctx, "k_tab_expect");
     k_tab_expect<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (size_t)ctx->nwords, a, st->alive, ctx->npad, per_traj, sd);
     QSB_LAUNCH_CHECK(ctx);
-    ctx->algo_bytes += (uint64_t)n * (2 * n + 2) * ctx->ntraj / 8; ctx->ops += ctx->ntraj;
+    qsb_account(ctx, "k_tab_expect", (uint64_t)n * (2 * n + 2) * ctx->ntraj / 8); ctx->ops += ctx->ntraj;
     if (stats_host) {
         QSB_CUDA(cudaMemcpyAsync(stats_host, sd, 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
         QSB_TRY(qsb_ctx_sync(ctx));

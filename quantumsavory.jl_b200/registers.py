@@ -260,8 +260,18 @@ class NonInstantGate:
         self.gate, self.duration = gate, duration
 
 
+def _normalize_mask(mask):
+    """A mask over a single trajectory is a plain Bool (the reference's scalar control flow)."""
+    if mask is None or isinstance(mask, bool):
+        return mask
+    if getattr(getattr(mask, "ctx", None), "ntraj", 0) == 1:
+        return bool(mask)
+    return mask
+
+
 def apply(refs, operation, time=None, mask=None):
     """apply!(refs, operation; time) -- src/baseops/apply.jl:10-23.  mask: per-trajectory condition."""
+    mask = _normalize_mask(mask)
     if isinstance(operation, NonInstantGate):
         _, new_time = apply(refs, operation.gate, time=time, mask=mask)
         uptotime(refs, new_time + operation.duration)
@@ -352,6 +362,7 @@ def traceout(*refs, mask=None):
     deleted per trajectory (that is the failed-purification case, CircuitZoo.jl:156-160); the slots
     stay assigned on the host and the state is marked dead on those lanes."""
     refs = [x for r in refs for x in (_refs(r))]
+    mask = _normalize_mask(mask)
     if mask is False:
         return tuple(r.reg for r in refs)
     requested = {(id(r.reg), r.idx) for r in refs}
