@@ -35,7 +35,9 @@ def wl_fgr(make_repr, formalism, record):
     from qsb200 import symbols as S
     from qsb200.workloads import firstgenrepeater as fgr
     bg = S.Depolarization(100.0) if formalism == "clifford" else S.T1T2Noise(1000.0, 100.0)
+    from qsb200.registers import dispose
     _, _, net = fgr.monte_carlo_trajectory(make_repr, background=bg, record=record, **FGR)
+    dispose(net.registers)
     return net.log
 
 
@@ -44,7 +46,7 @@ def wl_sweep12(make_repr, formalism, record, n=12, rounds=2, seed=11):
     qubit, project_traceout! of the last qubit, re-compose a fresh |0>."""
     from qsb200 import ops
     from qsb200 import symbols as S
-    from qsb200.registers import Register, apply, initialize, observable, project_traceout, uptotime
+    from qsb200.registers import Register, apply, dispose, initialize, observable, project_traceout, uptotime
     rng = np.random.default_rng(seed)
     reg = Register(n, make_repr(), S.T1T2Noise(100.0, 10.0))
     for i in range(1, n, 2):
@@ -63,6 +65,7 @@ def wl_sweep12(make_repr, formalism, record, n=12, rounds=2, seed=11):
         initialize(reg[n], time=t)
         apply((reg[n - 1], reg[n]), ops.CNOT)
         record("ZZ", t, observable((reg[1], reg[2]), ops.tensor(ops.Z, ops.Z)))
+    dispose([reg])
     return {"rounds": rounds, "n": n}
 
 
@@ -309,7 +312,8 @@ def main():
     ap.add_argument("--extras", default="firstgenrepeater_dm,sweep12_dm", help="extra workloads reported under 'extra' (N=1 only)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "b200" and not os.environ.get("QSB_PROFILING"):  # under ncu a short warm-up is fine; never for a reported number
+        args.warmup = max(args.warmup, 3)
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
     w = WORKLOADS[args.workload]

@@ -71,6 +71,7 @@ class BatchContext:
         check(self.L.qsb_ctx_reset_counters(self.p))
 
     def close(self):
+        """Destroys the context; every state / mask handle still alive is released with it."""
         if self.p:
             self.L.qsb_ctx_destroy(self.p)
             self.p = None
@@ -270,13 +271,18 @@ class CudaBatchState:
     def __init__(self, ctx: BatchContext, p):
         self.ctx, self.p = ctx, p
 
+    def free(self):
+        """Release the device memory now (the Julia finalizer's job; explicit here because register
+        <-> StateRef reference cycles would otherwise wait for Python's cycle collector)."""
+        if self.p and self.ctx.p:
+            self.ctx.L.qsb_state_free(self.p)
+        self.p = None
+
     def __del__(self):
         try:
-            if self.p and self.ctx.p:
-                self.ctx.L.qsb_state_free(self.p)
+            self.free()
         except Exception:
             pass
-        self.p = None
 
     # -- construction ----------------------------------------------------------------------------
     @classmethod

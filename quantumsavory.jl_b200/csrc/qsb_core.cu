@@ -98,9 +98,19 @@ extern "C" int qsb_ctx_profile_report(qsb_ctx* ctx, char* buf, size_t buflen) {
 int qsb_dev_alloc(qsb_ctx* ctx, void** p, size_t bytes) {
     if (bytes == 0) bytes = 16;
     cudaError_t e = cudaMallocAsync(p, bytes, ctx->stream);
+    if (e == cudaErrorMemoryAllocation) {
+        // the pool keeps freed blocks (release threshold = max): wait for pending frees, give them back, retry once
+        cudaGetLastError();
+        cudaStreamSynchronize(ctx->stream);
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+        e = cudaMallocAsync(p, bytes, ctx->stream);
+    }
     if (e != cudaSuccess) {
         cudaGetLastError();
-        qsb_set_error("cudaMallocAsync(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+        size_t fr = 0, tot = 0;
+        cudaMemGetInfo(&fr, &tot);
+        qsb_set_error("cudaMallocAsync(%zu bytes) failed: %s (device has %zu of %zu bytes free)", bytes, cudaGetErrorString(e), fr, tot);
         return e == cudaErrorMemoryAllocation ? QSB_ERR_OOM : QSB_ERR_CUDA;
     }
     return QSB_OK;
@@ -145,6 +155,7 @@ int qsb_state_alloc(qsb_ctx* ctx, int kind, int n, qsb_state** out) {
     int rc = qsb_dev_alloc(ctx, &st->data, st->bytes);
     if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&st->alive, ctx->nwords * sizeof(uint32_t));
     if (rc != QSB_OK) { qsb_dev_free(ctx, st->data); delete st; return rc; }
+    ctx->live_states->insert(st);
     *out = st;
     return QSB_OK;
 }
@@ -153,6 +164,7 @@ int qsb_mask_alloc(qsb_ctx* ctx, qsb_mask** out) {
     m->ctx = ctx; m->w = nullptr;
     int rc = qsb_dev_alloc(ctx, (void**)&m->w, ctx->nwords * sizeof(uint32_t));
     if (rc != QSB_OK) { delete m; return rc; }
+    ctx->live_masks->insert(m);
     *out = m;
     return QSB_OK;
 }
@@ -222,6 +234,8 @@ extern "C" int qsb_ctx_create(int device, int64_t ntraj, int64_t traj_offset, ui
     QSB_CUDA(cudaSetDevice(device));
     qsb_ctx* ctx = new qsb_ctx();
     memset(ctx, 0, sizeof(*ctx));
+    ctx->live_states = new std::set<qsb_state*>();
+    ctx->live_masks = new std::set<qsb_mask*>();
     ctx->device = device;
     ctx->ntraj = ntraj;
     ctx->npad = (ntraj + 31) / 32 * 32;
@@ -252,6 +266,9 @@ extern "C" int qsb_ctx_destroy(qsb_ctx* ctx) {
     if (!ctx) return QSB_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    for (qsb_state* s : *ctx->live_states) { cudaFreeAsync(s->data, ctx->stream); cudaFreeAsync(s->alive, ctx->stream); delete s; }
+    for (qsb_mask* m : *ctx->live_masks) { cudaFreeAsync(m->w, ctx->stream); delete m; }
+    delete ctx->live_states; delete ctx->live_masks;
     cudaFreeAsync(ctx->valid, ctx->stream);
     cudaFreeAsync(ctx->dev_flags, ctx->stream);
     cudaFreeAsync(ctx->stats_tmp, ctx->stream);
@@ -260,6 +277,8 @@ extern "C" int qsb_ctx_destroy(qsb_ctx* ctx) {
     if (ctx->obs_buf) cudaFreeAsync(ctx->obs_buf, ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->prof) qsb_ctx_profile(ctx, 0);
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return QSB_OK;
@@ -310,6 +329,7 @@ extern "C" int qsb_mask_create(qsb_ctx* ctx, int fill, qsb_mask** out) {
 }
 extern "C" int qsb_mask_free(qsb_mask* m) {
     if (!m) return QSB_OK;
+    m->ctx->live_masks->erase(m);
     int rc = qsb_dev_free(m->ctx, m->w);
     delete m;
     return rc;
@@ -430,6 +450,7 @@ extern "C" int qsb_state_copy(const qsb_state* st, qsb_state** out) {
 }
 extern "C" int qsb_state_free(qsb_state* st) {
     if (!st) return QSB_OK;
+    st->ctx->live_states->erase(st);
     int rc = qsb_dev_free(st->ctx, st->data);
     int rc2 = qsb_dev_free(st->ctx, st->alive);
     delete st;

@@ -159,20 +159,39 @@ int qsbd_to_host(const qsb_state* st, int64_t traj, double* out) {
 // =============================================================================================
 // subsystemcompose: out = a (x) b with a least significant (a3)
 // =============================================================================================
+// Each thread keeps a tile of up to TB elements of b in registers and streams a through it, so a and b are
+// read (about) once and the pass is bounded by the output write: 16*(4^na + 4^nb) read + 16*4^(na+nb) written.
+#define TENSOR_TB 16
 template <bool DM>
-__global__ void k_tensor(double2* out, const double2* __restrict__ a, const double2* __restrict__ b, int64_t npad, int na, int nb) {
+__global__ void __launch_bounds__(TPB) k_tensor(double2* __restrict__ out, const double2* __restrict__ a, const double2* __restrict__ b, int64_t npad, int na, int nb) {
     int64_t t = blockIdx.x * (int64_t)TPB + threadIdx.x;
     if (t >= npad) return;
     size_t Da = (size_t)1 << na, Db = (size_t)1 << nb;
     size_t La = DM ? Da * Da : Da, Lb = DM ? Db * Db : Db;
     int n = na + nb;
-    for (size_t ea = blockIdx.y; ea < La; ea += gridDim.y) {
-        double2 av = a[ea * npad + t];
-        size_t ra = DM ? (ea & (Da - 1)) : ea, ca = DM ? (ea >> na) : 0;
-        for (size_t eb = 0; eb < Lb; ++eb) {
-            size_t rb = DM ? (eb & (Db - 1)) : eb, cb = DM ? (eb >> nb) : 0;
-            size_t eo = DM ? ((ra | (rb << na)) + ((ca | (cb << na)) << n)) : (ra | (rb << na));
-            out[eo * npad + t] = cmul(av, b[eb * npad + t]);
+    size_t ntiles = (Lb + TENSOR_TB - 1) / TENSOR_TB;
+    // blockIdx.y walks (b tile, a chunk) pairs
+    size_t chunks = (gridDim.y + ntiles - 1) / ntiles;  // a-chunks per tile
+    if (chunks < 1) chunks = 1;
+    for (size_t job = blockIdx.y; job < ntiles * chunks; job += gridDim.y) {
+        size_t tile = job / chunks, chunk = job % chunks;
+        size_t eb0 = tile * TENSOR_TB;
+        double2 bv[TENSOR_TB];
+#pragma unroll
+        for (int j = 0; j < TENSOR_TB; ++j) bv[j] = (eb0 + j < Lb) ? b[(eb0 + j) * npad + t] : make_double2(0, 0);
+        size_t ea_lo = La * chunk / chunks, ea_hi = La * (chunk + 1) / chunks;
+        for (size_t ea = ea_lo; ea < ea_hi; ++ea) {
+            double2 av = a[ea * npad + t];
+            size_t ra = DM ? (ea & (Da - 1)) : ea, ca = DM ? (ea >> na) : 0;
+#pragma unroll
+            for (int j = 0; j < TENSOR_TB; ++j) {
+                size_t eb = eb0 + j;
+                if (eb < Lb) {
+                    size_t rb = DM ? (eb & (Db - 1)) : eb, cb = DM ? (eb >> nb) : 0;
+                    size_t eo = DM ? ((ra | (rb << na)) + ((ca | (cb << na)) << n)) : (ra | (rb << na));
+                    out[eo * npad + t] = cmul(av, bv[j]);
+                }
+            }
         }
     }
 }
@@ -190,7 +209,8 @@ int qsbd_tensor2(qsb_ctx* ctx, const qsb_state* a, const qsb_state* b, qsb_state
     qsb_state* st;
     QSB_TRY(qsb_state_alloc(ctx, kind, a->n + b->n, &st));
     size_t La = kind == QSB_DM ? (size_t)1 << (2 * a->n) : (size_t)1 << a->n;
-    Grid2 g = plan_grid(ctx, La);
+    size_t Lb = kind == QSB_DM ? (size_t)1 << (2 * b->n) : (size_t)1 << b->n;
+    Grid2 g = plan_grid(ctx, ((Lb + TENSOR_TB - 1) / TENSOR_TB) * La);
     QSB_PRE(ctx, "k_tensor");
     if (kind == QSB_DM) k_tensor<true><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, (const double2*)xa->data, (const double2*)xb->data, ctx->npad, a->n, b->n);
     else k_tensor<false><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, (const double2*)xa->data, (const double2*)xb->data, ctx->npad, a->n, b->n);

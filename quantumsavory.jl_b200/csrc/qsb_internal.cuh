@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <set>
 #include <string>
 #include <vector>
 
@@ -47,6 +48,8 @@ struct qsb_ctx {
     uint64_t launches, algo_bytes, ops, draws;
     int sm_count;
     struct qsb_prof* prof;  // per-kernel CUDA-event timing, off unless qsb_ctx_profile(ctx, 1)
+    std::set<struct qsb_state*>* live_states;  // handles not yet freed by the caller (released at destroy)
+    std::set<struct qsb_mask*>* live_masks;
 };
 
 struct qsb_state {

@@ -398,3 +398,16 @@ def project_traceout(ref: RegRef, basis, time=None, f=None):
     j, stateref.state = stateref.state.project_traceout(stateindex, basis)
     removebackref(stateref, stateindex)
     return f(j) if f is not None else j
+
+
+def dispose(registers):
+    """Drop every state the given registers still hold and release its backend memory at once."""
+    seen = set()
+    for reg in registers:
+        for i, s in enumerate(reg.staterefs):
+            if s is not None and id(s) not in seen:
+                seen.add(id(s))
+                if hasattr(s.state, "free"):
+                    s.state.free()
+            reg.staterefs[i] = None
+            reg.stateindices[i] = 0
