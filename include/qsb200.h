@@ -163,6 +163,23 @@ int qsb_mask_random(qsb_ctx* ctx, double p, uint64_t draw_id, qsb_mask** out); /
 int qsb_state_alive(const qsb_state* st, qsb_mask** out);
 int qsb_state_kill(qsb_state* st, const qsb_mask* lanes);
 
+/* ---- recorded programs (command buffer) ------------------------------------------------------------
+ * Between qsb_record_begin and qsb_record_end every call on the context is CAPTURED instead of launched
+ * (like a CUDA graph capture): handles created inside are virtual, host-visible calls (counts_host,
+ * stats_host, *_to_host, qsb_mask_count) are refused, and device pointers passed as stats_dev /
+ * per_traj_dev are captured by address.  Only Clifford (QSB_TAB) states can be recorded in this round.
+ * qsb_program_run executes the whole op list in ONE launch with each 32-trajectory word's tableaux
+ * resident in shared memory (a thread only ever touches its own word column, so no grid sync is needed
+ * between ops).  traj_shift re-bases the ensemble on fresh global trajectory ids (a new batch of the same
+ * schedule); draw_base offsets every draw id.  SURVEY.md 7.2 "command buffer", 8f-2. */
+typedef struct qsb_program qsb_program;
+int qsb_record_begin(qsb_ctx* ctx);
+int qsb_record_end(qsb_ctx* ctx, qsb_program** out);
+int qsb_program_run(qsb_program* prog, uint64_t traj_shift, uint64_t draw_base);
+/* info: {ops, arena planes, statistics rows, threads per block, shared bytes per block, 1 if arena in global memory} */
+int qsb_program_info(const qsb_program* prog, int64_t info[6]);
+int qsb_program_free(qsb_program* prog);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,6 +67,10 @@ class BatchContext:
         check(self.L.qsb_ctx_profile_report(self.p, buf, len(buf)))
         return json.loads(buf.value.decode())
 
+    def record(self):
+        """with ctx.record() as rec: ...issue the schedule once...; rec.program.run() replays it fused."""
+        return _Recording(self)
+
     def reset_counters(self):
         check(self.L.qsb_ctx_reset_counters(self.p))
 
@@ -85,6 +89,51 @@ class BatchContext:
         p = C.c_void_p()
         check(self.L.qsb_mask_random(self.p, float(prob), self.next_draw(), C.byref(p)))
         return BatchMask(self, p)
+
+
+class Program:
+    """A recorded op list (qsb_program): one fused launch per run()."""
+
+    def __init__(self, ctx, p):
+        self.ctx, self.p = ctx, p
+
+    def run(self, traj_shift: int = 0, draw_base: int = 0):
+        check(self.ctx.L.qsb_program_run(self.p, traj_shift, draw_base))
+
+    def info(self):
+        a = (C.c_int64 * 6)()
+        check(self.ctx.L.qsb_program_info(self.p, a))
+        return dict(zip(("ops", "planes", "stats_rows", "threads", "smem_bytes", "global_arena"), list(a)))
+
+    def free(self):
+        if self.p and self.ctx.p:
+            self.ctx.L.qsb_program_free(self.p)
+        self.p = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class _Recording:
+    def __init__(self, ctx):
+        self.ctx, self.program = ctx, None
+
+    def __enter__(self):
+        check(self.ctx.L.qsb_record_begin(self.ctx.p))
+        return self
+
+    def __exit__(self, et, ev, tb):
+        p = C.c_void_p()
+        rc = self.ctx.L.qsb_record_end(self.ctx.p, C.byref(p))
+        if et is None:
+            check(rc)
+            self.program = Program(self.ctx, p)
+        elif rc == 0:
+            self.ctx.L.qsb_program_free(p)
+        return False
 
 
 class BatchMask:
@@ -402,7 +451,8 @@ class CudaBatchState:
         check(self.ctx.L.qsb_ptrace(self.p, int(idx) - 1, self.ctx.next_draw() if self.kind == MCKET else 0))
         return self
 
-    def observable(self, indices, obs, per_trajectory: bool = False, stats_dev: int | None = None, sync: bool = True):
+    def observable(self, indices, obs, per_trajectory: bool = False, stats_dev: int | None = None, sync: bool = True,
+                   per_traj_dev: int | None = None):
         """-> BatchValue.  stats_dev: optional device pointer (double[4]) that receives the statistics
         without a host sync (sync=False), e.g. a torch tensor that is NCCL-all-reduced later."""
         ctx = self.ctx
@@ -426,7 +476,7 @@ class CudaBatchState:
             mat = obs.mat if isinstance(obs, ops.Gate) else np.asarray(obs, dtype=np.complex128)
             buf = _colmajor_ri(mat)
             kind, ptr, keep = _lib.OBS_OP, buf.ctypes.data_as(C.c_void_p), buf
-        per_dev = None
+        per_dev = C.c_void_p(per_traj_dev) if per_traj_dev else None
         per_t = None
         if per_trajectory:
             import torch

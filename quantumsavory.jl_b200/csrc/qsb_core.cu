@@ -151,7 +151,16 @@ int qsb_state_alloc(qsb_ctx* ctx, int kind, int n, qsb_state** out) {
     qsb_state* st = new qsb_state();
     st->ctx = ctx; st->kind = kind; st->n = n;
     st->bytes = qsb_state_bytes(ctx, kind, n);
-    st->data = nullptr; st->alive = nullptr;
+    st->data = nullptr; st->alive = nullptr; st->vbase = st->valive = -1; st->gen = 0;
+    if (ctx->rec) {
+        if (kind != QSB_TAB) { delete st; QSB_FAIL(QSB_ERR_UNSUPPORTED, "only Clifford (tableau) states can be recorded into a program"); }
+        st->vbase = qsb_rec_alloc_planes(ctx, qsb_tab_planes(n));
+        st->valive = qsb_rec_alloc_planes(ctx, 1);
+        st->gen = ctx->rec_gen;
+        ctx->live_states->insert(st);
+        *out = st;
+        return QSB_OK;
+    }
     int rc = qsb_dev_alloc(ctx, &st->data, st->bytes);
     if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&st->alive, ctx->nwords * sizeof(uint32_t));
     if (rc != QSB_OK) { qsb_dev_free(ctx, st->data); delete st; return rc; }
@@ -161,7 +170,13 @@ int qsb_state_alloc(qsb_ctx* ctx, int kind, int n, qsb_state** out) {
 }
 int qsb_mask_alloc(qsb_ctx* ctx, qsb_mask** out) {
     qsb_mask* m = new qsb_mask();
-    m->ctx = ctx; m->w = nullptr;
+    m->ctx = ctx; m->w = nullptr; m->vplane = -1; m->gen = 0;
+    if (ctx->rec) {
+        m->vplane = qsb_rec_alloc_planes(ctx, 1); m->gen = ctx->rec_gen;
+        ctx->live_masks->insert(m);
+        *out = m;
+        return QSB_OK;
+    }
     int rc = qsb_dev_alloc(ctx, (void**)&m->w, ctx->nwords * sizeof(uint32_t));
     if (rc != QSB_OK) { delete m; return rc; }
     ctx->live_masks->insert(m);
@@ -218,6 +233,17 @@ __global__ void k_kill(uint32_t* alive, const uint32_t* lanes, int64_t nwords) {
 }
 
 static inline unsigned wgrid(int64_t nwords) { return (unsigned)((nwords + 255) / 256); }
+
+int qsb_handle_ok(const qsb_ctx* ctx, bool is_virtual, int gen) {
+    if (ctx->rec) {
+        if (!is_virtual) QSB_FAIL(QSB_ERR_BAD_ARG, "a handle created outside the recording cannot be used inside it");
+        if (gen != ctx->rec_gen) QSB_FAIL(QSB_ERR_BAD_ARG, "handle belongs to an earlier recording");
+    } else if (is_virtual) QSB_FAIL(QSB_ERR_BAD_ARG, "handle belongs to a recorded program and has no storage of its own");
+    return QSB_OK;
+}
+#define ST_OK(st) QSB_TRY(qsb_handle_ok((st)->ctx, (st)->vbase >= 0, (st)->gen))
+#define MK_OK(m) QSB_TRY(qsb_handle_ok((m)->ctx, (m)->vplane >= 0, (m)->gen))
+#define NO_REC(ctx, what) do { if ((ctx)->rec) QSB_FAIL(QSB_ERR_UNSUPPORTED, what " is host-visible and cannot be recorded"); } while (0)
 
 // ---------------------------------------------------------------------------------------------
 // context
@@ -321,6 +347,7 @@ extern "C" int qsb_mask_create(qsb_ctx* ctx, int fill, qsb_mask** out) {
     if (!ctx || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     qsb_mask* m;
     QSB_TRY(qsb_mask_alloc(ctx, &m));
+    if (ctx->rec) { TabOp* op = qsb_rec_push(ctx, TOP_MASK_FILL); op->m[0] = m->vplane; op->iv[0] = fill; *out = m; return QSB_OK; }
     QSB_PRE(ctx, "k_mask_fill");
     k_mask_fill<<<wgrid(ctx->nwords), 256, 0, ctx->stream>>>(m->w, ctx->valid, ctx->nwords, fill);
     QSB_LAUNCH_CHECK(ctx);
@@ -330,6 +357,7 @@ extern "C" int qsb_mask_create(qsb_ctx* ctx, int fill, qsb_mask** out) {
 extern "C" int qsb_mask_free(qsb_mask* m) {
     if (!m) return QSB_OK;
     m->ctx->live_masks->erase(m);
+    if (m->vplane >= 0) { if (m->ctx->rec && m->gen == m->ctx->rec_gen) qsb_rec_free_planes(m->ctx, m->vplane, 1); delete m; return QSB_OK; }
     int rc = qsb_dev_free(m->ctx, m->w);
     delete m;
     return rc;
@@ -337,6 +365,8 @@ extern "C" int qsb_mask_free(qsb_mask* m) {
 extern "C" int qsb_mask_logic(qsb_mask* dst, const qsb_mask* a, const qsb_mask* b, int op) {
     if (!dst || !a || (op != QSB_MASK_NOT && !b)) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_mask_logic: null operand");
     qsb_ctx* ctx = dst->ctx;
+    MK_OK(dst); MK_OK(a); if (b) MK_OK(b);
+    if (ctx->rec) { TabOp* o = qsb_rec_push(ctx, TOP_MASK_LOGIC); o->m[0] = dst->vplane; o->m[1] = a->vplane; o->m[2] = b ? b->vplane : -1; o->iv[0] = op; return QSB_OK; }
     QSB_PRE(ctx, "k_mask_logic");
     k_mask_logic<<<wgrid(ctx->nwords), 256, 0, ctx->stream>>>(dst->w, a->w, b ? b->w : nullptr, ctx->valid, ctx->nwords, op);
     QSB_LAUNCH_CHECK(ctx);
@@ -345,6 +375,7 @@ extern "C" int qsb_mask_logic(qsb_mask* dst, const qsb_mask* a, const qsb_mask* 
 extern "C" int qsb_mask_count(const qsb_mask* m, int64_t* out) {
     if (!m || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     qsb_ctx* ctx = m->ctx;
+    NO_REC(ctx, "qsb_mask_count"); MK_OK(m);
     QSB_CUDA(cudaMemsetAsync(ctx->counts_tmp, 0, sizeof(long long), ctx->stream));
     unsigned g = wgrid(ctx->nwords); if (g > 1024) g = 1024;
     QSB_PRE(ctx, "k_mask_count");
@@ -358,6 +389,7 @@ extern "C" int qsb_mask_count(const qsb_mask* m, int64_t* out) {
 }
 extern "C" int qsb_mask_to_host(const qsb_mask* m, uint32_t* words) {
     if (!m || !words) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
+    NO_REC(m->ctx, "qsb_mask_to_host"); MK_OK(m);
     QSB_CUDA(cudaMemcpyAsync(words, m->w, m->ctx->nwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, m->ctx->stream));
     QSB_CUDA(cudaStreamSynchronize(m->ctx->stream));
     return QSB_OK;
@@ -365,6 +397,7 @@ extern "C" int qsb_mask_to_host(const qsb_mask* m, uint32_t* words) {
 extern "C" int qsb_mask_from_host(qsb_mask* m, const uint32_t* words) {
     if (!m || !words) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     qsb_ctx* ctx = m->ctx;
+    NO_REC(ctx, "qsb_mask_from_host"); MK_OK(m);
     QSB_CUDA(cudaMemcpyAsync(m->w, words, ctx->nwords * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
     QSB_PRE(ctx, "k_mask_logic");
     k_mask_logic<<<wgrid(ctx->nwords), 256, 0, ctx->stream>>>(m->w, m->w, m->w, ctx->valid, ctx->nwords, QSB_MASK_AND);
@@ -375,6 +408,7 @@ extern "C" int qsb_mask_random(qsb_ctx* ctx, double p, uint64_t draw_id, qsb_mas
     if (!ctx || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     qsb_mask* m;
     QSB_TRY(qsb_mask_alloc(ctx, &m));
+    if (ctx->rec) { TabOp* o = qsb_rec_push(ctx, TOP_MASK_RANDOM); o->m[0] = m->vplane; o->f[0] = p; o->draw = draw_id; ctx->draws++; *out = m; return QSB_OK; }
     QSB_PRE(ctx, "k_mask_random");
     k_mask_random<<<(unsigned)((ctx->npad + 255) / 256), 256, 0, ctx->stream>>>(m->w, ctx->valid, ctx->npad, ctx->seed, (uint64_t)ctx->traj_offset, draw_id, p);
     QSB_LAUNCH_CHECK(ctx);
@@ -384,8 +418,10 @@ extern "C" int qsb_mask_random(qsb_ctx* ctx, double p, uint64_t draw_id, qsb_mas
 }
 extern "C" int qsb_state_alive(const qsb_state* st, qsb_mask** out) {
     if (!st || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
+    ST_OK(st);
     qsb_mask* m;
     QSB_TRY(qsb_mask_alloc(st->ctx, &m));
+    if (st->ctx->rec) { TabOp* o = qsb_rec_push(st->ctx, TOP_ALIVE_COPY); o->m[0] = m->vplane; o->al[0] = st->valive; *out = m; return QSB_OK; }
     QSB_CUDA(cudaMemcpyAsync(m->w, st->alive, st->ctx->nwords * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st->ctx->stream));
     *out = m;
     return QSB_OK;
@@ -393,6 +429,8 @@ extern "C" int qsb_state_alive(const qsb_state* st, qsb_mask** out) {
 extern "C" int qsb_state_kill(qsb_state* st, const qsb_mask* lanes) {
     if (!st || !lanes) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     qsb_ctx* ctx = st->ctx;
+    ST_OK(st); MK_OK(lanes);
+    if (ctx->rec) { TabOp* o = qsb_rec_push(ctx, TOP_KILL); o->al[0] = st->valive; o->m[0] = lanes->vplane; return QSB_OK; }
     QSB_PRE(ctx, "k_kill");
     k_kill<<<wgrid(ctx->nwords), 256, 0, ctx->stream>>>(st->alive, lanes->w, ctx->nwords);
     QSB_LAUNCH_CHECK(ctx);
@@ -404,6 +442,7 @@ extern "C" int qsb_state_kill(qsb_state* st, const qsb_mask* lanes) {
 // ---------------------------------------------------------------------------------------------
 static int check_idx(const qsb_state* st, const int* idx, int k) {
     if (!st) QSB_FAIL(QSB_ERR_BAD_ARG, "null state");
+    ST_OK(st);
     if (k < 1 || k > st->n) QSB_FAIL(QSB_ERR_BAD_INDEX, "%d indices given for a state of %d subsystems", k, st->n);
     for (int a = 0; a < k; ++a) {
         if (idx[a] < 0 || idx[a] >= st->n) QSB_FAIL(QSB_ERR_BAD_INDEX, "subsystem index %d out of range for a state of %d subsystems", idx[a] + 1, st->n);
@@ -435,14 +474,20 @@ extern "C" int qsb_state_select(qsb_ctx* ctx, const qsb_state* const* states, co
     for (int i = 0; i < m; ++i) {
         if (!states[i] || states[i]->ctx != ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_state_select: state %d is null or from another context", i);
         if (states[i]->kind != states[0]->kind || states[i]->n != states[0]->n) QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_state_select: all states must share kind and size");
+        ST_OK(states[i]);
     }
     ctx->draws++;
     return states[0]->kind == QSB_TAB ? qsbt_select(ctx, states, weights, m, draw_id, out) : qsbd_select(ctx, states, weights, m, draw_id, out);
 }
 extern "C" int qsb_state_copy(const qsb_state* st, qsb_state** out) {
     if (!st || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
+    ST_OK(st);
     qsb_state* c;
     QSB_TRY(qsb_state_alloc(st->ctx, st->kind, st->n, &c));
+    if (st->ctx->rec) {
+        TabOp* o = qsb_rec_push(st->ctx, TOP_COPY); o->n = st->n; o->s[0] = c->vbase; o->s[1] = st->vbase; o->al[0] = c->valive; o->al[1] = st->valive;
+        *out = c; return QSB_OK;
+    }
     QSB_CUDA(cudaMemcpyAsync(c->data, st->data, st->bytes, cudaMemcpyDeviceToDevice, st->ctx->stream));
     QSB_CUDA(cudaMemcpyAsync(c->alive, st->alive, st->ctx->nwords * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st->ctx->stream));
     *out = c;
@@ -451,6 +496,10 @@ extern "C" int qsb_state_copy(const qsb_state* st, qsb_state** out) {
 extern "C" int qsb_state_free(qsb_state* st) {
     if (!st) return QSB_OK;
     st->ctx->live_states->erase(st);
+    if (st->vbase >= 0) {
+        if (st->ctx->rec && st->gen == st->ctx->rec_gen) { qsb_rec_free_planes(st->ctx, st->vbase, qsb_tab_planes(st->n)); qsb_rec_free_planes(st->ctx, st->valive, 1); }
+        delete st; return QSB_OK;
+    }
     int rc = qsb_dev_free(st->ctx, st->data);
     int rc2 = qsb_dev_free(st->ctx, st->alive);
     delete st;
@@ -467,19 +516,21 @@ extern "C" int qsb_state_promote_dm(qsb_state* st) {
 extern "C" int qsb_state_to_host(const qsb_state* st, int64_t traj, double* out) {
     if (!st || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     if (traj < 0 || traj >= st->ctx->ntraj) QSB_FAIL(QSB_ERR_BAD_INDEX, "trajectory %lld out of range", (long long)traj);
+    NO_REC(st->ctx, "qsb_state_to_host"); ST_OK(st);
     if (!qsb_is_dense(st->kind)) QSB_FAIL(QSB_ERR_UNSUPPORTED, "use qsb_tab_to_host for tableaux");
     return qsbd_to_host(st, traj, out);
 }
 extern "C" int qsb_tab_to_host(const qsb_state* st, int64_t traj, uint8_t* xs, uint8_t* zs, uint8_t* signs, uint8_t* active) {
     if (!st) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     if (traj < 0 || traj >= st->ctx->ntraj) QSB_FAIL(QSB_ERR_BAD_INDEX, "trajectory %lld out of range", (long long)traj);
+    NO_REC(st->ctx, "qsb_tab_to_host"); ST_OK(st);
     if (st->kind != QSB_TAB) QSB_FAIL(QSB_ERR_UNSUPPORTED, "not a tableau");
     return qsbt_to_host(st, traj, xs, zs, signs, active);
 }
 
 extern "C" int qsb_tensor(qsb_ctx* ctx, const qsb_state* const* states, int m, qsb_state** out) {
     if (!ctx || !states || m < 1 || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_tensor: bad argument");
-    for (int i = 0; i < m; ++i) if (!states[i] || states[i]->ctx != ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_tensor: state %d is null or from another context", i);
+    for (int i = 0; i < m; ++i) { if (!states[i] || states[i]->ctx != ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_tensor: state %d is null or from another context", i); ST_OK(states[i]); }
     bool any_tab = false, all_tab = true;
     for (int i = 0; i < m; ++i) { any_tab |= states[i]->kind == QSB_TAB; all_tab &= states[i]->kind == QSB_TAB; }
     if (any_tab && !all_tab) QSB_FAIL(QSB_ERR_UNSUPPORTED, "subsystemcompose has no method for a tableau and a dense state");
@@ -521,6 +572,7 @@ extern "C" int qsb_measure(qsb_state* st, int idx, int basis, const double* kets
     QSB_TRY(check_idx(st, &idx, 1));
     if (!outcome2) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_measure: outcome2 must not be null");
     qsb_ctx* ctx = st->ctx;
+    if (ctx->rec && counts_host) QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_measure with counts_host is host-visible and cannot be recorded");
     qsb_mask *o = nullptr, *r = nullptr;
     QSB_TRY(qsb_mask_alloc(ctx, &o));
     int rc;
@@ -553,6 +605,7 @@ extern "C" int qsb_expect(qsb_state* st, const int* idx, int k, int obs_kind, co
                           double* per_traj, double* stats_dev, double* stats_host) {
     QSB_TRY(check_idx(st, idx, k));
     if (!obs) QSB_FAIL(QSB_ERR_BAD_ARG, "null observable");
+    if (st->ctx->rec && stats_host) QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_expect with stats_host is host-visible and cannot be recorded; pass stats_dev");
     if (st->kind == QSB_TAB) return qsbt_expect(st, idx, k, obs_kind, obs, obs_sign, per_traj, stats_dev, stats_host);
     return qsbd_expect(st, idx, k, obs_kind, obs, obs_sign, per_traj, stats_dev, stats_host);
 }

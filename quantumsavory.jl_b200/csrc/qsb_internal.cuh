@@ -50,6 +50,8 @@ struct qsb_ctx {
     struct qsb_prof* prof;  // per-kernel CUDA-event timing, off unless qsb_ctx_profile(ctx, 1)
     std::set<struct qsb_state*>* live_states;  // handles not yet freed by the caller (released at destroy)
     std::set<struct qsb_mask*>* live_masks;
+    struct qsb_recorder* rec;  // non-null between qsb_record_begin and qsb_record_end
+    int rec_gen;
 };
 
 struct qsb_state {
@@ -59,11 +61,15 @@ struct qsb_state {
     void* data;       // double2* or uint32_t*
     size_t bytes;
     uint32_t* alive;  // [nwords]
+    int vbase, valive; // record mode: plane indices inside the program arena (data == alive == nullptr)
+    int gen;           // recording generation the virtual planes belong to
 };
 
 struct qsb_mask {
     qsb_ctx* ctx;
     uint32_t* w;
+    int vplane;        // record mode: plane index inside the program arena (w == nullptr)
+    int gen;
 };
 
 // ---- error plumbing ---------------------------------------------------------------------------
@@ -121,6 +127,32 @@ int qsbt_measure(qsb_state* st, int idx, int basis, uint64_t draw_id, qsb_mask* 
 int qsbt_ptrace(qsb_state* st, int idx);
 int qsbt_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* obs, int obs_sign,
                 double* per_traj, double* stats_dev, double* stats_host);
+
+// ---- recorded programs (qsb_exec.cu): tableau op lists executed by ONE fused launch ----------------
+enum { TOP_INIT, TOP_TENSOR, TOP_SELECT, TOP_COPY, TOP_GATE, TOP_NOISE, TOP_MEASURE, TOP_PTRACE, TOP_FORCE, TOP_EXPECT,
+       TOP_MASK_FILL, TOP_MASK_LOGIC, TOP_MASK_RANDOM, TOP_KILL, TOP_ALIVE_COPY };
+struct TabOp {
+    int type, n, n2, k;
+    int s[6];       // state base planes (s[0] is the destination where there is one)
+    int al[6];      // alive planes matching s[]
+    int m[3];       // mask planes (-1: none)
+    int q[2];
+    int iv[4];
+    uint32_t u[2], lut;
+    uint8_t outmask[4];
+    double f[8];
+    uint64_t draw;
+    double* stats;      // absolute device pointers captured at record time
+    double* per_traj;
+    int obs;            // index into the program's TabObsArgs table
+};
+int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes);
+void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes);
+TabOp* qsb_rec_push(qsb_ctx* ctx, int type);           // zero-initialised op with all plane refs = -1
+int qsb_rec_push_obs(qsb_ctx* ctx, const void* tab_obs_args, size_t bytes);
+void qsb_rec_note_stats(qsb_ctx* ctx, double* p);
+// a handle is usable when it is real outside a recording, or virtual and owned by the active recording
+int qsb_handle_ok(const qsb_ctx* ctx, bool is_virtual, int gen);
 
 // ---- device helpers ---------------------------------------------------------------------------
 #ifdef __CUDACC__

@@ -27,6 +27,7 @@ __global__ void k_tab_init(uint32_t* p, uint32_t* alive, const uint32_t* valid, 
 int qsbt_new(qsb_ctx* ctx, int n, int active, qsb_state** out) {
     qsb_state* st;
     QSB_TRY(qsb_state_alloc(ctx, QSB_TAB, n, &st));
+    if (ctx->rec) { TabOp* o = qsb_rec_push(ctx, TOP_INIT); o->n = n; o->s[0] = st->vbase; o->al[0] = st->valive; o->iv[0] = active; *out = st; return QSB_OK; }
     QSB_PRE(ctx, "k_tab_init");
     k_tab_init<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, st->alive, ctx->valid, (size_t)ctx->nwords, n, active);
     QSB_LAUNCH_CHECK(ctx);
@@ -45,6 +46,11 @@ int qsbt_tensor2(qsb_ctx* ctx, const qsb_state* a, const qsb_state* b, qsb_state
     if (a->n + b->n > MAXN) QSB_FAIL(QSB_ERR_UNSUPPORTED, "composite tableau would exceed %d qubits", MAXN);
     qsb_state* st;
     QSB_TRY(qsb_state_alloc(ctx, QSB_TAB, a->n + b->n, &st));
+    if (ctx->rec) {
+        TabOp* o = qsb_rec_push(ctx, TOP_TENSOR); o->n = a->n; o->n2 = b->n;
+        o->s[0] = st->vbase; o->s[1] = a->vbase; o->s[2] = b->vbase; o->al[0] = st->valive; o->al[1] = a->valive; o->al[2] = b->valive;
+        ctx->ops += ctx->ntraj; *out = st; return QSB_OK;
+    }
     QSB_PRE(ctx, "k_tab_tensor");
     k_tab_tensor<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, st->alive, (const uint32_t*)a->data, (const uint32_t*)b->data, a->alive, b->alive,
                                                        (size_t)ctx->nwords, a->n, b->n);
@@ -83,6 +89,13 @@ int qsbt_select(qsb_ctx* ctx, const qsb_state* const* states, const double* w, i
     double total = 0, cum = 0;
     for (int i = 0; i < m; ++i) total += w[i];
     for (int i = 0; i < m; ++i) { cum += w[i] / total; a.cum[i] = cum; a.src[i] = (const uint32_t*)states[i]->data; a.alive[i] = states[i]->alive; }
+    if (ctx->rec) {
+        if (m > 5) { qsb_state_free(st); QSB_FAIL(QSB_ERR_UNSUPPORTED, "recorded mixtures are limited to 5 states"); }
+        TabOp* o = qsb_rec_push(ctx, TOP_SELECT); o->n = st->n; o->n2 = m; o->draw = draw_id;
+        o->s[0] = st->vbase; o->al[0] = st->valive;
+        for (int i = 0; i < m; ++i) { o->s[1 + i] = states[i]->vbase; o->al[1 + i] = states[i]->valive; o->f[i] = a.cum[i]; }
+        ctx->ops += ctx->ntraj; *out = st; return QSB_OK;
+    }
     QSB_PRE(ctx, "k_tab_select");
     k_tab_select<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, st->alive, a, (size_t)ctx->nwords, qsb_tab_planes(st->n), ctx->seed, (uint64_t)ctx->traj_offset, draw_id);
     QSB_LAUNCH_CHECK(ctx);
@@ -135,6 +148,13 @@ int qsbt_apply(qsb_state* st, const int* idx, int k, const uint8_t* table, const
     }
     if (table[0] != 0) QSB_FAIL(QSB_ERR_BAD_ARG, "conjugation table maps the identity to a non-identity");
     for (int b = 0; b < nb; ++b) for (int j = 0; j < nb; ++j) if ((cols[j] >> b) & 1) a.outmask[b] |= 1 << j;
+    if (mask) QSB_TRY(qsb_handle_ok(ctx, mask->vplane >= 0, mask->gen));
+    if (ctx->rec) {
+        TabOp* o = qsb_rec_push(ctx, TOP_GATE); o->n = a.n; o->k = a.k; o->q[0] = a.q[0]; o->q[1] = a.q[1]; o->lut = a.lut;
+        for (int j = 0; j < 4; ++j) o->outmask[j] = a.outmask[j];
+        o->s[0] = st->vbase; o->m[0] = mask ? mask->vplane : -1;
+        ctx->ops += ctx->ntraj; return QSB_OK;
+    }
     QSB_PRE(ctx, "k_tab_gate");
     k_tab_gate<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (size_t)ctx->nwords, a, mask ? mask->w : nullptr);
     QSB_LAUNCH_CHECK(ctx);
@@ -148,7 +168,7 @@ int qsbt_apply(qsb_state* st, const int* idx, int k, const uint8_t* table, const
 __global__ void k_tab_noise(uint32_t* p, size_t W, TabNoiseArgs a, uint64_t seed, uint64_t traj0, uint64_t draw_id) {
     size_t w = blockIdx.x * (size_t)TTPB + threadIdx.x;
     if (w >= W) return;
-    tab_noise_word(p, W, w, a, seed, traj0, draw_id);
+    tab_noise_word(p, W, w, w, a, seed, traj0, draw_id);
 }
 int qsbt_channel(qsb_state* st, int idx, int bg, const double* prm, double dt, uint64_t draw_id) {
     qsb_ctx* ctx = st->ctx;
@@ -161,6 +181,11 @@ int qsbt_channel(qsb_state* st, int idx, int bg, const double* prm, double dt, u
     else QSB_FAIL(QSB_ERR_UNSUPPORTED, "no paulinoise method for this background on a Clifford state (reference raises MethodError)");
     double cum = 1.0;
     for (int i = 0; i < a.np; ++i) { cum -= probs[i]; a.cum[i] = cum; }
+    if (ctx->rec) {
+        TabOp* o = qsb_rec_push(ctx, TOP_NOISE); o->n = a.n; o->q[0] = a.q; o->k = a.np; o->draw = draw_id; o->s[0] = st->vbase;
+        for (int j = 0; j < 3; ++j) { o->f[j] = a.cum[j]; o->iv[j] = a.op[j]; }
+        ctx->ops += ctx->ntraj; ctx->draws++; return QSB_OK;
+    }
     QSB_PRE(ctx, "k_tab_noise");
     k_tab_noise<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (size_t)ctx->nwords, a, ctx->seed, (uint64_t)ctx->traj_offset, draw_id);
     QSB_LAUNCH_CHECK(ctx);
@@ -176,7 +201,7 @@ __global__ void k_tab_measure(uint32_t* in, uint32_t* out, size_t W, int n, int 
     size_t w = blockIdx.x * (size_t)TTPB + threadIdx.x;
     if (w >= W) return;
     uint32_t rnd;
-    uint32_t outcome = tab_measure_word(in, out, W, w, n, q, tx, tz, seed, traj0, draw_id, &rnd);
+    uint32_t outcome = tab_measure_word(in, out, W, w, w, n, q, tx, tz, seed, traj0, draw_id, &rnd);
     uint32_t al = alive[w];
     outcome2[w] = outcome & al;
     if (was_random) was_random[w] = rnd & al;
@@ -209,6 +234,14 @@ int qsbt_measure(qsb_state* st, int idx, int basis, uint64_t draw_id, qsb_mask* 
     qsb_ctx* ctx = st->ctx;
     int n = st->n;
     int tx = (basis == QSB_BASIS_X || basis == QSB_BASIS_Y), tz = (basis == QSB_BASIS_Z || basis == QSB_BASIS_Y);
+    if (ctx->rec) {
+        int nb = qsb_rec_alloc_planes(ctx, qsb_tab_planes(n - 1));
+        TabOp* o = qsb_rec_push(ctx, TOP_MEASURE); o->n = n; o->q[0] = idx; o->iv[0] = tx; o->iv[1] = tz; o->draw = draw_id;
+        o->s[0] = nb; o->s[1] = st->vbase; o->al[1] = st->valive; o->m[0] = outcome2->vplane; o->m[1] = was_random ? was_random->vplane : -1;
+        qsb_rec_free_planes(ctx, st->vbase, qsb_tab_planes(n));
+        st->vbase = nb; st->n = n - 1; st->bytes = qsb_state_bytes(ctx, QSB_TAB, n - 1);
+        ctx->ops += ctx->ntraj; return QSB_OK;
+    }
     void* nd;
     QSB_TRY(qsb_dev_alloc(ctx, &nd, qsb_state_bytes(ctx, QSB_TAB, n - 1)));
     if (counts_host) QSB_CUDA(cudaMemsetAsync(ctx->counts_tmp, 0, 3 * sizeof(long long), ctx->stream));
@@ -229,6 +262,13 @@ int qsbt_measure(qsb_state* st, int idx, int basis, uint64_t draw_id, qsb_mask* 
 int qsbt_ptrace(qsb_state* st, int idx) {
     qsb_ctx* ctx = st->ctx;
     int n = st->n;
+    if (ctx->rec) {
+        int nb = qsb_rec_alloc_planes(ctx, qsb_tab_planes(n - 1));
+        TabOp* o = qsb_rec_push(ctx, TOP_PTRACE); o->n = n; o->q[0] = idx; o->s[0] = nb; o->s[1] = st->vbase;
+        qsb_rec_free_planes(ctx, st->vbase, qsb_tab_planes(n));
+        st->vbase = nb; st->n = n - 1; st->bytes = qsb_state_bytes(ctx, QSB_TAB, n - 1);
+        ctx->ops += ctx->ntraj; return QSB_OK;
+    }
     void* nd;
     QSB_TRY(qsb_dev_alloc(ctx, &nd, qsb_state_bytes(ctx, QSB_TAB, n - 1)));
     QSB_PRE(ctx, "k_tab_ptrace");
@@ -250,6 +290,7 @@ int qsbt_from_host(qsb_ctx* ctx, int n, int ngen, const uint8_t* xs, const uint8
         uint32_t px = 0, pz = 0;
         for (int q = 0; q < n; ++q) { if (xs[g * n + q]) px |= 1u << q; if (zs[g * n + q]) pz |= 1u << q; }
         if ((px | pz) == 0) { qsb_state_free(st); QSB_FAIL(QSB_ERR_BAD_ARG, "stabilizer generator %d is the identity", g + 1); }
+        if (ctx->rec) { TabOp* o = qsb_rec_push(ctx, TOP_FORCE); o->n = n; o->s[0] = st->vbase; o->u[0] = px; o->u[1] = pz; o->iv[0] = signs ? signs[g] : 0; continue; }
         QSB_PRE(ctx, "k_tab_force");
         k_tab_force<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (size_t)ctx->nwords, n, px, pz, signs ? signs[g] : 0);
         QSB_LAUNCH_CHECK(ctx);
@@ -333,6 +374,12 @@ int qsbt_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* 
         }
     } else {
         QSB_FAIL(QSB_ERR_UNSUPPORTED, "dense observables on a Clifford state are not implemented (the reference converts a pure tableau to a ket, clifford/express.jl:22-46)");
+    }
+    if (ctx->rec) {
+        TabOp* o = qsb_rec_push(ctx, TOP_EXPECT); o->n = n; o->s[0] = st->vbase; o->al[0] = st->valive;
+        o->obs = qsb_rec_push_obs(ctx, &a, sizeof(a)); o->stats = stats_dev; o->per_traj = per_traj;
+        qsb_rec_note_stats(ctx, stats_dev);
+        ctx->ops += ctx->ntraj; return QSB_OK;
     }
     double* sd = stats_dev ? stats_dev : ((stats_host) ? ctx->stats_tmp : nullptr);
     if (sd) QSB_CUDA(cudaMemsetAsync(sd, 0, 4 * sizeof(double), ctx->stream));

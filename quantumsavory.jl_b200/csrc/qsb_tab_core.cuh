@@ -305,10 +305,10 @@ QSB_HD void tab_gate_word(uint32_t* p, size_t W, size_t w, const TabGateArgs& a,
 }
 
 struct TabNoiseArgs { int n, q, np; double cum[3]; int op[3]; /* 1 X, 2 Y, 3 Z */ };
-QSB_HD void tab_noise_word(uint32_t* p, size_t W, size_t w, const TabNoiseArgs& a, uint64_t seed, uint64_t traj0, uint64_t draw_id) {
+QSB_HD void tab_noise_word(uint32_t* p, size_t W, size_t w, size_t wg, const TabNoiseArgs& a, uint64_t seed, uint64_t traj0, uint64_t draw_id) {
     uint32_t fx = 0, fz = 0;  // lanes receiving a Pauli with X / Z component
     for (int l = 0; l < 32; ++l) {
-        double r = qsb_draw(seed, traj0 + (uint64_t)(w * 32 + l), draw_id);
+        double r = qsb_draw(seed, traj0 + (uint64_t)(wg * 32 + l), draw_id);
         for (int i = 0; i < a.np; ++i) {
             if (r > a.cum[i]) {
                 int P = a.op[i];
@@ -328,11 +328,11 @@ QSB_HD void tab_noise_word(uint32_t* p, size_t W, size_t w, const TabNoiseArgs& 
 
 // project_traceout! on a tableau (a9): projectremoverand!(state, projectX!/Y!/Z!, idx).
 // returns the outcome word (bit = 1 for outcome 2); *rnd = lanes whose outcome consumed the draw.
-QSB_HD uint32_t tab_measure_word(uint32_t* in, uint32_t* out, size_t W, size_t w, int n, int q, int tx, int tz,
+QSB_HD uint32_t tab_measure_word(uint32_t* in, uint32_t* out, size_t W, size_t w, size_t wg, int n, int q, int tx, int tz,
                                  uint64_t seed, uint64_t traj0, uint64_t draw_id, uint32_t* rnd) {
     TabView v = make_view(in, W, w, n), o = make_view(out, W, w, n - 1);
     Analysis A;
-    uint32_t rbits = lane_bits_ge_half(seed, traj0, w, draw_id);
+    uint32_t rbits = lane_bits_ge_half(seed, traj0, wg, draw_id);
     uint32_t outcome = project_update(v, (uint32_t)tx << q, (uint32_t)tz << q, rbits, true, A);
     *rnd = A.found;
     if (n > 1) remove_qubit(v, o, q, A, outcome, 0u);

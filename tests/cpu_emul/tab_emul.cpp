@@ -45,12 +45,12 @@ void et_noise(ETab* t, int q, int np, const double* cum, const int* op, uint64_t
     TabNoiseArgs a; memset(&a, 0, sizeof(a));
     a.n = t->n; a.q = q; a.np = np;
     for (int i = 0; i < np; ++i) { a.cum[i] = cum[i]; a.op[i] = op[i]; }
-    for (size_t w = 0; w < t->W; ++w) tab_noise_word(t->p.data(), t->W, w, a, seed, traj0, draw_id);
+    for (size_t w = 0; w < t->W; ++w) tab_noise_word(t->p.data(), t->W, w, w, a, seed, traj0, draw_id);
 }
 void et_measure(ETab* t, int q, int tx, int tz, uint64_t seed, uint64_t traj0, uint64_t draw_id, uint32_t* outcome2, uint32_t* rnd) {
     int n = t->n;
     std::vector<uint32_t> o((size_t)planes(n - 1) * t->W + 4, 0);
-    for (size_t w = 0; w < t->W; ++w) outcome2[w] = tab_measure_word(t->p.data(), o.data(), t->W, w, n, q, tx, tz, seed, traj0, draw_id, &rnd[w]);
+    for (size_t w = 0; w < t->W; ++w) outcome2[w] = tab_measure_word(t->p.data(), o.data(), t->W, w, w, n, q, tx, tz, seed, traj0, draw_id, &rnd[w]);
     t->p.swap(o); t->n = n - 1;
 }
 void et_ptrace(ETab* t, int q) {
