@@ -226,6 +226,28 @@ class GpuRun:
         self.keys = keys
         return log
 
+    def record_program(self):
+        """Runs the host schedule ONCE in record mode (nothing launches) and keeps the fused program.
+        Later steps replay it on fresh trajectory ids: the classical schedule is shared by the ensemble."""
+        t0 = time.perf_counter()
+        with self.ctx.record() as rec:
+            log = self.step()
+        self.program = rec.program
+        self.program_log = log
+        self.record_ms = 1e3 * (time.perf_counter() - t0)
+        self.batch = 0
+        return log
+
+    def upload_program(self):
+        with self.torch.cuda.stream(self.stream):
+            self.h2d_bytes = self.program.upload()
+
+    def run_program(self):
+        """One fused launch over a fresh batch of ntraj trajectories per GPU (global ids never repeat)."""
+        self.batch += 1
+        self.program.run(traj_shift=self.batch * self.ntraj * self.world)
+        return self.program_log
+
     def finish_step(self):
         """The step's result crosses GPUs (one all-reduce) and comes back to the host (D2H)."""
         with self.torch.cuda.stream(self.stream):
@@ -234,11 +256,18 @@ class GpuRun:
         return host.numpy()
 
 
-def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, profile=True):
+def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, profile=True, mode="per_op"):
+    """mode "per_op": every backend call is one launch (the drop-in path, host schedule re-run each step).
+    mode "program": the schedule is recorded once (untimed, reported as record_ms) and each step replays it as
+    ONE fused launch on a fresh batch of trajectories; e2e additionally re-sends the op list from the host."""
     import torch
     import torch.distributed as dist
     g = GpuRun(workload, ntraj, rank, world, local_rank)
     ctx = g.ctx
+    program = mode == "program"
+    if program:
+        g.record_program()
+    do_step = g.run_program if program else g.step
 
     def barrier():
         if world > 1:
@@ -246,7 +275,7 @@ def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, pr
         torch.cuda.synchronize()
 
     for _ in range(warmup):
-        g.step(); g.finish_step()
+        do_step(); g.finish_step()
     barrier()
     ctx.reset_counters()
     sampler = ClockSampler(local_rank)
@@ -258,8 +287,11 @@ def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, pr
     for _ in range(steps):
         with torch.cuda.stream(g.stream):
             g.flush.zero_()                       # flush L2 between timed iterations (not timed on the device clock)
+        if program:
+            g.upload_program()                    # host op list -> device: inside e2e, before the device-timed region
+        with torch.cuda.stream(g.stream):
             ev0.record(g.stream)
-        log = g.step()
+        log = do_step()
         with torch.cuda.stream(g.stream):
             ev1.record(g.stream)
         host_stats = g.finish_step()              # e2e: all-reduce + D2H of the step's result
@@ -277,10 +309,12 @@ def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, pr
                value=ntraj * world * steps / (dev_ms / 1e3), e2e=ntraj * world * steps / (wall_ms / 1e3),
                launches_per_step=counters["launches"] / steps, algo_bytes_per_step=counters["algo_bytes"] / steps,
                ops_per_step=counters["ops"] / steps, nobs=g.nobs, d2h_bytes=g.nobs * 32, clocks=clocks, log=log,
-               sample_stats=host_stats[: min(4, len(host_stats))].tolist())
+               sample_stats=host_stats[: min(4, len(host_stats))].tolist(), mode=mode, h2d_bytes=g.h2d_bytes)
+    if program:
+        out["program"] = dict(g.program.info(), record_ms=g.record_ms)
     if profile and rank == 0:
         ctx.profile(True)
-        g.step(); g.finish_step()
+        do_step(); g.finish_step()
         rows = ctx.profile_report()
         ctx.profile(False)
         rows = [r for r in rows if r["launches"]]
@@ -297,6 +331,13 @@ def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, pr
                            "frac": top["gbs"] / peak, "traffic": None, "peak_source": which,
                            "algo_bytes_per_launch": top["algo_bytes"] / top["launches"], "us_per_launch": top["us_per_launch"],
                            "share_of_step": top["share"]}
+        if program:
+            info = out["program"]
+            sec = top["ms"] * 1e-3 / top["launches"]
+            out["roofline"]["note"] = ("fused launch: the ensemble's tableaux stay in shared memory, so compulsory HBM traffic is only the op list, "
+                                       "the valid words and the statistics rows; the kernel is integer-ALU bound (Philox4x32-10 draws), see alu")
+            out["roofline"]["alu"] = {"philox_draws_per_s": info["draws"] * ntraj / sec, "state_ops_per_s": info["state_ops"] / sec,
+                                      "draws_per_trajectory": info["draws"], "recorded_ops": info["ops"]}
     ctx.close()
     return out
 
@@ -311,6 +352,8 @@ def main():
     ap.add_argument("--ntraj", type=int, default=0, help="trajectories per GPU (default: the config's)")
     ap.add_argument("--extras", default="firstgenrepeater_dm,sweep12_dm", help="extra workloads reported under 'extra' (N=1 only)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--mode", default="auto", choices=["auto", "per_op", "program"],
+                    help="program: recorded op list replayed as one fused launch (Clifford workloads); per_op: one launch per backend call")
     args = ap.parse_args()
     if args.impl == "b200" and not os.environ.get("QSB_PROFILING"):  # under ncu a short warm-up is fine; never for a reported number
         args.warmup = max(args.warmup, 3)
@@ -347,13 +390,25 @@ def main():
     import torch.distributed as dist
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    main_res = run_gpu_workload(args.workload, ntraj, args.steps, args.warmup, rank, world, local_rank)
+    mode = args.mode if args.mode != "auto" else ("program" if w["formalism"] == "clifford" else "per_op")
+    if mode == "program" and w["formalism"] != "clifford":
+        raise SystemExit("only Clifford workloads can be recorded into a fused program in this round")
+    config["mode"] = ("recorded program: host schedule captured once (untimed, program.record_ms), every step = ONE fused launch over a fresh batch of trajectories"
+                      if mode == "program" else "per-op: host schedule re-run every step, one launch per backend call")
+    main_res = run_gpu_workload(args.workload, ntraj, args.steps, args.warmup, rank, world, local_rank, mode=mode)
     extra = {}
+    keep = ("ntraj_per_gpu", "dev_ms_per_step", "value", "e2e", "launches_per_step", "algo_bytes_per_step", "ops_per_step", "roofline", "kernels", "mode")
+    if world == 1 and mode == "program" and args.extras:
+        try:  # the same workload through the per-call drop-in path, for comparison
+            r = run_gpu_workload(args.workload, ntraj, max(2, min(args.steps, 3)), 3, 0, 1, local_rank, mode="per_op")
+            extra[args.workload + "_per_op"] = {k: r[k] for k in keep if k in r}
+        except Exception as e:
+            extra[args.workload + "_per_op"] = {"error": repr(e)[:300]}
     if world == 1 and args.extras:
         for name in [x for x in args.extras.split(",") if x and x != args.workload]:
             try:
                 r = run_gpu_workload(name, WORKLOADS[name]["ntraj"], max(2, min(args.steps, 3)), 3, 0, 1, local_rank)
-                extra[name] = {k: r[k] for k in ("ntraj_per_gpu", "dev_ms_per_step", "value", "e2e", "launches_per_step", "algo_bytes_per_step", "ops_per_step", "roofline", "kernels") if k in r}
+                extra[name] = {k: r[k] for k in keep if k in r}
                 extra[name]["state_ops_per_sec"] = r["ops_per_step"] / (r["dev_ms_per_step"] * 1e-3)
             except Exception as e:  # an extra must never take the headline down
                 extra[name] = {"error": repr(e)[:300]}
@@ -368,8 +423,10 @@ def main():
                 "warmup": args.warmup, "ms_per_step": main_res["dev_ms_per_step"], "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u32 bit-sliced tableau" if w["formalism"] == "clifford" else "f64 complex", "data": "synthetic",
                 "config": config, "clocks": main_res["clocks"],
-                "e2e": {"value": main_res["e2e"], "unit": "trajectories/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": main_res["d2h_bytes"],
-                        "note": "wall clock around the public API calls incl. the all-reduce + D2H of the step's statistics; inputs are host-side symbols/matrices passed by value through the C-ABI"},
+                "e2e": {"value": main_res["e2e"], "unit": "trajectories/s", "h2d_bytes_per_step": main_res["h2d_bytes"], "d2h_bytes_per_step": main_res["d2h_bytes"],
+                        "note": ("wall clock around upload of the host op list (pinned) + qsb_program_run + all-reduce + D2H of the step's statistics" if mode == "program" else
+                                 "wall clock around the public API calls incl. the all-reduce + D2H of the step's statistics; inputs are host-side symbols/matrices passed by value through the C-ABI")},
+                "program": main_res.get("program"),
                 "gpu_launches": int(main_res["launches_per_step"] * args.steps),
                 "state_ops_per_sec": main_res["ops_per_step"] * world / (main_res["dev_ms_per_step"] * 1e-3),
                 "roofline": main_res.get("roofline"), "kernels": main_res.get("kernels"), "cpu_baseline": cpu,

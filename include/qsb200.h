@@ -176,8 +176,11 @@ typedef struct qsb_program qsb_program;
 int qsb_record_begin(qsb_ctx* ctx);
 int qsb_record_end(qsb_ctx* ctx, qsb_program** out);
 int qsb_program_run(qsb_program* prog, uint64_t traj_shift, uint64_t draw_base);
-/* info: {ops, arena planes, statistics rows, threads per block, shared bytes per block, 1 if arena in global memory} */
-int qsb_program_info(const qsb_program* prog, int64_t info[6]);
+/* re-sends the recorded op list (the program's only host-side input) to the device, async on the stream */
+int qsb_program_upload(qsb_program* prog, int64_t* bytes);
+/* info: {ops, arena planes, statistics rows, threads per block, shared bytes per block, 1 if arena in global memory,
+ *        register-state ops per run summed over trajectories, draws per run} */
+int qsb_program_info(const qsb_program* prog, int64_t info[8]);
 int qsb_program_free(qsb_program* prog);
 
 #ifdef __cplusplus

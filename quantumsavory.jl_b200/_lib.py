@@ -102,6 +102,7 @@ def _declare(L):
         "qsb_record_end": (C.c_int, [vp, vpp]),
         "qsb_program_run": (C.c_int, [vp, C.c_uint64, C.c_uint64]),
         "qsb_program_info": (C.c_int, [vp, i64p]),
+        "qsb_program_upload": (C.c_int, [vp, i64p]),
         "qsb_program_free": (C.c_int, [vp]),
         "qsb_state_alive": (C.c_int, [vp, vpp]),
         "qsb_state_kill": (C.c_int, [vp, vp]),

@@ -100,10 +100,16 @@ class Program:
     def run(self, traj_shift: int = 0, draw_base: int = 0):
         check(self.ctx.L.qsb_program_run(self.p, traj_shift, draw_base))
 
+    def upload(self) -> int:
+        """Re-sends the host op list to the device (async H2D); returns the bytes copied."""
+        b = C.c_int64()
+        check(self.ctx.L.qsb_program_upload(self.p, C.byref(b)))
+        return b.value
+
     def info(self):
-        a = (C.c_int64 * 6)()
+        a = (C.c_int64 * 8)()
         check(self.ctx.L.qsb_program_info(self.p, a))
-        return dict(zip(("ops", "planes", "stats_rows", "threads", "smem_bytes", "global_arena"), list(a)))
+        return dict(zip(("ops", "planes", "stats_rows", "threads", "smem_bytes", "global_arena", "state_ops", "draws"), list(a)))
 
     def free(self):
         if self.p and self.ctx.p:

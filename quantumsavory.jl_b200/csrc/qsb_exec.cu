@@ -6,6 +6,12 @@
 // its own 32-trajectory word column of every plane, so consecutive ops need no grid synchronisation:
 // one thread can run the complete op list on its column.  The arena (all live states and masks of the
 // schedule, planes allocated/recycled at record time) is a [planes][blockDim] tile of shared memory.
+//
+// Lanes per thread: this translation unit compiles the tableau core with 8-lane BYTE planes (QSB_PLANE_T), so an
+// ensemble of N trajectories runs on N/8 threads instead of N/32 -- the bit logic is latency bound (dependent
+// shared-memory round trips), and 10^6 trajectories are only 977 warps of 32-lane words on 148 SMs.
+#define QSB_PLANE_T uint8_t
+#define QSB_CORE_NS tabcore8
 #include <map>
 
 #include "qsb_internal.cuh"
@@ -17,16 +23,29 @@ struct qsb_recorder {
     std::vector<double*> stats_ptrs;
     int next_plane = 0, high = 0;
     std::multimap<int, int> free_blocks;  // size -> base
+    uint64_t ops0 = 0, draws0 = 0;        // context counters at qsb_record_begin (recording itself executes nothing)
+};
+
+// one stochastic op of the program as the draw pass sees it
+struct DrawSpec {
+    uint64_t draw;
+    int type, np, slot, pad;   // type: TOP_NOISE / TOP_SELECT / TOP_MEASURE / TOP_MASK_RANDOM
+    double cum[5];
+    int op[3];
 };
 
 struct qsb_program {
     qsb_ctx* ctx;
+    DrawSpec* d_specs; int nspecs, nslots;
+    uint32_t* bits;        // [nslots][nwords] decision words written by k_draw_bits, read by k_tab_exec
     TabOp* d_ops; int nops;
     TabObsArgs* d_obs; int nobs;
     double** d_stats; int nstats;
     int planes;
-    uint32_t* arena;       // global-memory arena, only when the shared-memory tile does not fit
+    plane_t* arena;        // global-memory arena, only when the shared-memory tile does not fit
     int threads, smem_bytes;
+    TabOp* h_ops;          // pinned host copy of the op list (qsb_program_upload re-sends it)
+    uint64_t ops_per_run, draws_per_run, per_traj_rows;
 };
 
 int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes) {
@@ -41,7 +60,10 @@ int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes) {
     }
     int base = R->next_plane;
     R->next_plane += nplanes;
-    if (R->next_plane > R->high) R->high = R->next_plane;
+    if (R->next_plane > R->high) {
+        R->high = R->next_plane;
+        if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] op %zu: high-water %d planes (block of %d)\n", R->ops.size(), R->high, nplanes);
+    }
     return base;
 }
 void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes) {
@@ -58,6 +80,11 @@ void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes) {
     }
     if (base + nplanes == R->next_plane) R->next_plane = base;
     else R->free_blocks.insert({nplanes, base});
+}
+void qsb_rec_shrink(qsb_ctx* ctx, int base, int old_planes, int new_planes) {
+    if (old_planes <= 0) old_planes = 1;
+    if (new_planes <= 0) new_planes = 1;   // a 0-qubit state keeps one (unused) plane, like a fresh allocation would
+    if (new_planes < old_planes) qsb_rec_free_planes(ctx, base + new_planes, old_planes - new_planes);
 }
 TabOp* qsb_rec_push(qsb_ctx* ctx, int type) {
     TabOp op;
@@ -82,9 +109,10 @@ int qsb_rec_push_obs(qsb_ctx* ctx, const void* a, size_t bytes) {
 struct ExecArgs {
     const TabOp* ops; int nops;
     const TabObsArgs* obs;
-    uint32_t* arena;          // nullptr -> shared-memory tile
-    const uint32_t* valid;
-    size_t W;                 // words in the ensemble
+    plane_t* arena;           // nullptr -> shared-memory tile
+    const plane_t* bits;      // decision bits of every stochastic op, [slot][W] (the draw pass's words seen lane-group wise)
+    const plane_t* valid;
+    size_t W;                 // lane groups (threads) in the ensemble = trajectories / QSB_LANES
     uint64_t seed, traj0, draw_base;
 };
 
@@ -93,24 +121,72 @@ __global__ void k_zero_stats(double* const* ptrs, int n) {
     if (i < n) { double* p = ptrs[i]; p[0] = 0; p[1] = 0; p[2] = 0; p[3] = 0; }
 }
 
-__global__ void k_tab_exec(ExecArgs a) {
-    extern __shared__ uint32_t tile[];
-    const size_t wg = blockIdx.x * (size_t)blockDim.x + threadIdx.x;  // global word (trajectories 32*wg ..)
+// Draw pass: ONE THREAD PER TRAJECTORY evaluates every stochastic op's Philox draw and its decision; a warp
+// ballot packs the 32 decisions of a word, so the bit-sliced pass below never runs Philox (which a
+// thread-per-word kernel would have to loop over its 32 lanes for, at 1/32 of the parallelism).
+__global__ void __launch_bounds__(256) k_draw_bits(const DrawSpec* __restrict__ specs, int nspecs, uint32_t* __restrict__ bits,
+                                                   size_t W, uint64_t seed, uint64_t traj0, uint64_t draw_base) {
+    const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;   // local trajectory; W*32 is a multiple of 32
+    if (t >= W * 32) return;                                          // whole warps leave together
+    const size_t wg = t >> 5;
+    const unsigned lane = threadIdx.x & 31u;
+    const uint64_t traj = traj0 + t;
+    for (int i = 0; i < nspecs; ++i) {
+        const DrawSpec& s = specs[i];
+        const double u = qsb_draw(seed, traj, s.draw + draw_base);
+        uint32_t d;
+        if (s.type == TOP_NOISE) {
+            d = 0;
+            for (int j = 0; j < s.np; ++j) if (u > s.cum[j]) { int P = s.op[j]; d = ((P == 1 || P == 2) ? 1u : 0u) | ((P == 3 || P == 2) ? 2u : 0u); break; }
+        } else if (s.type == TOP_SELECT) {
+            d = (uint32_t)(s.np - 1);
+            for (int j = 0; j < s.np; ++j) if (s.cum[j] > u) { d = (uint32_t)j; break; }
+        } else if (s.type == TOP_MEASURE) {
+            d = u >= 0.5 ? 1u : 0u;
+        } else {
+            d = u < s.cum[0] ? 1u : 0u;
+        }
+        const uint32_t b0 = __ballot_sync(0xffffffffu, d & 1u);
+        uint32_t* dst = bits + (size_t)s.slot * W + wg;
+        if (s.type == TOP_NOISE) {
+            const uint32_t b1 = __ballot_sync(0xffffffffu, d & 2u);
+            if (lane == 0) { dst[0] = b0; dst[W] = b1; }
+        } else if (s.type == TOP_SELECT) {
+            const uint32_t b1 = __ballot_sync(0xffffffffu, d & 2u), b2 = __ballot_sync(0xffffffffu, d & 4u);
+            if (lane == 0) { dst[0] = b0; dst[W] = b1; dst[2 * W] = b2; }
+        } else if (lane == 0) dst[0] = b0;
+    }
+}
+
+// The tableau functions are force-inlined with a LITERAL qubit count so that their loops unroll and their
+// per-row scratch arrays live in registers (a run-time n keeps them in local memory: 2.2 KB of stack per thread).
+#define N_CASE(K, ...) case K: { constexpr int N = K; __VA_ARGS__; } break;
+#define N_SWITCH(NV, ...) switch (NV) { N_CASE(1, __VA_ARGS__) N_CASE(2, __VA_ARGS__) N_CASE(3, __VA_ARGS__) N_CASE(4, __VA_ARGS__) \
+                                        N_CASE(5, __VA_ARGS__) default: { const int N = (NV); __VA_ARGS__; } break; }
+
+// T > 0: the arena is a [planes][T] tile of shared memory (block of T threads, compile-time stride);
+// T == 0: the arena is in global memory with stride a.W (programs whose tile exceeds the shared memory of an SM).
+template <int T>
+__global__ void __launch_bounds__(T ? T : 128) k_tab_exec(ExecArgs a) {
+    extern __shared__ plane_t tile[];
+    const size_t wg = blockIdx.x * (size_t)blockDim.x + threadIdx.x;  // global lane group (trajectories QSB_LANES*wg ..)
     const bool on = wg < a.W;
-    uint32_t* base; size_t W, w;
-    if (a.arena) { base = a.arena; W = a.W; w = on ? wg : 0; }
-    else { base = tile; W = blockDim.x; w = threadIdx.x; }
+    plane_t* const base = T ? tile : a.arena;
+    const size_t W = T ? (size_t)T : a.W;
+    const size_t w = T ? (size_t)threadIdx.x : (on ? wg : 0);
     const uint32_t validw = on ? a.valid[wg] : 0u;
 #define PL(idx) (base + (size_t)(idx) * W)
     for (int i = 0; i < a.nops; ++i) {
         const TabOp& op = a.ops[i];
-        const uint64_t draw = op.draw + a.draw_base;
         switch (op.type) {
         case TOP_INIT:
-            if (on) { tab_init_word(PL(op.s[0]), W, w, op.n, op.iv[0]); PL(op.al[0])[w] = validw; }
+            if (on) { N_SWITCH(op.n, tab_init_word(PL(op.s[0]), W, w, N, op.iv[0])) PL(op.al[0])[w] = validw; }
             break;
         case TOP_TENSOR:
-            if (on) { tab_tensor_word(PL(op.s[0]), PL(op.s[1]), PL(op.s[2]), W, w, op.n, op.n2); PL(op.al[0])[w] = PL(op.al[1])[w] & PL(op.al[2])[w]; }
+            if (on) {
+                if (op.n == 2 && op.n2 == 2) tab_tensor_word(PL(op.s[0]), PL(op.s[1]), PL(op.s[2]), W, w, 2, 2);
+                else tab_tensor_word(PL(op.s[0]), PL(op.s[1]), PL(op.s[2]), W, w, op.n, op.n2);
+                PL(op.al[0])[w] = PL(op.al[1])[w] & PL(op.al[2])[w]; }
             break;
         case TOP_COPY:
             if (on) {
@@ -121,13 +197,10 @@ __global__ void k_tab_exec(ExecArgs a) {
             break;
         case TOP_SELECT:
             if (on) {
-                uint32_t m[5] = {0, 0, 0, 0, 0};
-                for (int l = 0; l < 32; ++l) {
-                    double u = qsb_draw(a.seed, a.traj0 + (uint64_t)(wg * 32 + l), draw);
-                    int sel = op.n2 - 1;
-                    for (int j = 0; j < op.n2; ++j) if (op.f[j] > u) { sel = j; break; }
-                    m[sel] |= 1u << l;
-                }
+                uint32_t m[5];
+                const plane_t* d = a.bits + (size_t)op.dslot * a.W + wg;
+                const uint32_t b0 = d[0], b1 = d[a.W], b2 = d[2 * a.W];   // bit planes of the selected index
+                for (int j = 0; j < 5; ++j) m[j] = ((j & 1) ? b0 : ~b0) & ((j & 2) ? b1 : ~b1) & ((j & 4) ? b2 : ~b2);
                 int planes = op.n * (4 * op.n + 2);
                 for (int p = 0; p < planes; ++p) {
                     uint32_t v = 0;
@@ -143,45 +216,47 @@ __global__ void k_tab_exec(ExecArgs a) {
             if (on) {
                 TabGateArgs g; g.n = op.n; g.k = op.k; g.q[0] = op.q[0]; g.q[1] = op.q[1]; g.lut = op.lut;
                 for (int j = 0; j < 4; ++j) g.outmask[j] = op.outmask[j];
-                tab_gate_word(PL(op.s[0]), W, w, g, op.m[0] >= 0 ? PL(op.m[0])[w] : 0xFFFFFFFFu);
+                const uint32_t gm = op.m[0] >= 0 ? (uint32_t)PL(op.m[0])[w] : QSB_FULL;
+                N_SWITCH(op.n, g.n = N; tab_gate_word(PL(op.s[0]), W, w, g, gm))
             }
             break;
         case TOP_NOISE:
             if (on) {
-                TabNoiseArgs g; g.n = op.n; g.q = op.q[0]; g.np = op.k;
-                for (int j = 0; j < 3; ++j) { g.cum[j] = op.f[j]; g.op[j] = op.iv[j]; }
-                tab_noise_word(PL(op.s[0]), W, w, wg, g, a.seed, a.traj0, draw);
+                const plane_t* d = a.bits + (size_t)op.dslot * a.W + wg;
+                const uint32_t fx = d[0], fz = d[a.W];
+                N_SWITCH(op.n, tab_noise_apply(PL(op.s[0]), W, w, N, op.q[0], fx, fz))
             }
             break;
         case TOP_MEASURE:
             if (on) {
                 uint32_t rnd;
-                uint32_t outcome = tab_measure_word(PL(op.s[1]), PL(op.s[0]), W, w, wg, op.n, op.q[0], op.iv[0], op.iv[1], a.seed, a.traj0, draw, &rnd);
+                uint32_t outcome = 0; const uint32_t rb = a.bits[(size_t)op.dslot * a.W + wg];
+                N_SWITCH(op.n, outcome = tab_measure_bits(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0], op.iv[0], op.iv[1], rb, &rnd))
                 uint32_t al = PL(op.al[1])[w];
                 PL(op.m[0])[w] = outcome & al;
                 if (op.m[1] >= 0) PL(op.m[1])[w] = rnd & al;
             }
             break;
         case TOP_PTRACE:
-            if (on) tab_ptrace_word(PL(op.s[1]), PL(op.s[0]), W, w, op.n, op.q[0]);
+            if (on) { N_SWITCH(op.n, tab_ptrace_word(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0])) }
             break;
         case TOP_FORCE:
-            if (on) tab_force_word(PL(op.s[0]), W, w, op.n, op.u[0], op.u[1], op.iv[0]);
+            if (on) { N_SWITCH(op.n, tab_force_word(PL(op.s[0]), W, w, N, op.u[0], op.u[1], op.iv[0])) }
             break;
         case TOP_EXPECT: {
             double s_alive = 0, s_v = 0, s_v2 = 0;
             if (on) {
                 const TabObsArgs& o = a.obs[op.obs];
                 uint32_t cnt[8], cntm[8];
-                tab_expect_word(PL(op.s[0]), W, w, o, cnt, cntm);
+                N_SWITCH(op.n, tab_expect_word_n(PL(op.s[0]), W, w, N, o, cnt, cntm))
                 uint32_t al = PL(op.al[0])[w];
                 double inv = 1.0 / (double)o.nelem;
-                for (int l = 0; l < 32; ++l) {
+                for (int l = 0; l < QSB_LANES; ++l) {
                     int plus = 0, minus = 0;
                     for (int b = 0; b < 8; ++b) { plus |= ((cnt[b] >> l) & 1) << b; minus |= ((cntm[b] >> l) & 1) << b; }
                     bool lane = (al >> l) & 1u;
                     double val = lane ? (double)(plus - minus) * inv : 0.0;
-                    if (op.per_traj) { size_t t = wg * 32 + l; op.per_traj[2 * t] = val; op.per_traj[2 * t + 1] = 0.0; }
+                    if (op.per_traj) { size_t t = wg * QSB_LANES + l; op.per_traj[2 * t] = val; op.per_traj[2 * t + 1] = 0.0; }
                     if (lane) { s_alive += 1.0; s_v += val; s_v2 += val * val; }
                 }
             }
@@ -209,18 +284,16 @@ __global__ void k_tab_exec(ExecArgs a) {
                     case QSB_MASK_NOT: r = ~x; break;
                     default: r = ~(x ^ y); break;
                 }
-                PL(op.m[0])[w] = r & validw;
+                PL(op.m[0])[w] = (plane_t)(r & validw);
             }
             break;
         case TOP_MASK_RANDOM:
             if (on) {
-                uint32_t r = 0;
-                for (int l = 0; l < 32; ++l) if (qsb_draw(a.seed, a.traj0 + (uint64_t)(wg * 32 + l), draw) < op.f[0]) r |= 1u << l;
-                PL(op.m[0])[w] = r & validw;
+                PL(op.m[0])[w] = a.bits[(size_t)op.dslot * a.W + wg] & validw;
             }
             break;
         case TOP_KILL:
-            if (on) PL(op.al[0])[w] &= ~PL(op.m[0])[w];
+            if (on) PL(op.al[0])[w] = (plane_t)(PL(op.al[0])[w] & ~PL(op.m[0])[w]);
             break;
         case TOP_ALIVE_COPY:
             if (on) PL(op.m[0])[w] = PL(op.al[0])[w];
@@ -230,6 +303,17 @@ __global__ void k_tab_exec(ExecArgs a) {
 #undef PL
 }
 
+typedef void (*exec_fn)(ExecArgs);
+static exec_fn exec_kernel(int threads, bool global_arena) {
+    if (global_arena) return k_tab_exec<0>;
+    switch (threads) {
+        case 64: return k_tab_exec<64>;
+        case 128: return k_tab_exec<128>;
+        case 256: return k_tab_exec<256>;
+        default: return nullptr;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // C-ABI: record / run
 // ---------------------------------------------------------------------------------------------
@@ -237,6 +321,7 @@ extern "C" int qsb_record_begin(qsb_ctx* ctx) {
     if (!ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "null context");
     if (ctx->rec) QSB_FAIL(QSB_ERR_BAD_ARG, "already recording");
     ctx->rec = new qsb_recorder();
+    ctx->rec->ops0 = ctx->ops; ctx->rec->draws0 = ctx->draws;
     ctx->rec_gen++;
     return QSB_OK;
 }
@@ -250,7 +335,28 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     P->ctx = ctx;
     P->nops = (int)R->ops.size(); P->nobs = (int)R->obs.size(); P->nstats = (int)R->stats_ptrs.size();
     P->planes = R->high > 0 ? R->high : 1;
+    P->ops_per_run = ctx->ops - R->ops0; P->draws_per_run = ctx->draws - R->draws0;
+    ctx->ops = R->ops0; ctx->draws = R->draws0;  // counted per qsb_program_run instead
+    for (auto& o : R->ops) if (o.per_traj) P->per_traj_rows++;
     int rc = QSB_OK;
+    // stochastic ops -> draw specs + decision-word slots (noise: fx,fz; mixture: 3 index planes; others: 1)
+    std::vector<DrawSpec> specs;
+    for (auto& o : R->ops) {
+        int need = o.type == TOP_NOISE ? 2 : o.type == TOP_SELECT ? 3 : (o.type == TOP_MEASURE || o.type == TOP_MASK_RANDOM) ? 1 : 0;
+        if (!need) continue;
+        DrawSpec d; memset(&d, 0, sizeof(d));
+        d.draw = o.draw; d.type = o.type; d.slot = P->nslots;
+        d.np = o.type == TOP_NOISE ? o.k : o.type == TOP_SELECT ? o.n2 : 1;
+        for (int j = 0; j < 5; ++j) d.cum[j] = o.f[j];
+        for (int j = 0; j < 3; ++j) d.op[j] = o.iv[j];
+        o.dslot = P->nslots; P->nslots += need;
+        specs.push_back(d);
+    }
+    P->nspecs = (int)specs.size();
+    if (!R->ops.empty()) {
+        if (cudaMallocHost((void**)&P->h_ops, R->ops.size() * sizeof(TabOp)) != cudaSuccess) { cudaGetLastError(); qsb_set_error("pinned allocation of the op list failed"); rc = QSB_ERR_OOM; }
+        else memcpy(P->h_ops, R->ops.data(), R->ops.size() * sizeof(TabOp));
+    }
     auto up = [&](void** dst, const void* src, size_t bytes) {
         if (rc != QSB_OK) return;
         rc = qsb_dev_alloc(ctx, dst, bytes ? bytes : 16);
@@ -262,36 +368,40 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     up((void**)&P->d_ops, R->ops.data(), R->ops.size() * sizeof(TabOp));
     up((void**)&P->d_obs, R->obs.data(), R->obs.size() * sizeof(TabObsArgs));
     up((void**)&P->d_stats, R->stats_ptrs.data(), R->stats_ptrs.size() * sizeof(double*));
+    up((void**)&P->d_specs, specs.data(), specs.size() * sizeof(DrawSpec));
+    if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->bits, (size_t)(P->nslots ? P->nslots : 1) * ctx->nwords * sizeof(uint32_t));
     if (rc == QSB_OK) { cudaError_t e = cudaStreamSynchronize(ctx->stream); if (e != cudaSuccess) rc = QSB_ERR_CUDA; }  // host vectors die below
     // launch shape: the largest block whose [planes][threads] tile fits, preferring a single wave
     int dev_smem = 0;
     cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
+    const long groups = (long)ctx->nwords * (32 / QSB_LANES);   // one thread per lane group
     int best_t = 0; double best_cost = 1e300;
-    for (int t = 32; t <= 256; t += 32) {
-        size_t smem = (size_t)P->planes * t * sizeof(uint32_t);
+    for (int t = 64; t <= 256; t *= 2) {
+        size_t smem = (size_t)P->planes * t * sizeof(plane_t);
         if (smem > (size_t)dev_smem) break;
         int per_sm = (int)((size_t)(228 * 1024) / (smem + 1024));
         if (per_sm < 1) per_sm = 1;
+        if (per_sm > 32) per_sm = 32;
         if (per_sm * t > 2048) per_sm = 2048 / t;
-        long blocks = (long)((ctx->nwords + t - 1) / t);
+        long blocks = (groups + t - 1) / t;
         long slots = (long)ctx->sm_count * per_sm;
         long waves = (blocks + slots - 1) / slots;
-        // a wave costs about one thread's serial time; fewer resident warps per SM run faster per warp
-        double cost = (double)waves * (1.0 + 0.02 * per_sm * t / 32.0);
+        // a wave costs about one thread's serial time; more resident warps per SM stretch it only a little
+        double cost = (double)waves * (1.0 + 0.01 * per_sm * t / 32.0);
         if (cost < best_cost) { best_cost = cost; best_t = t; }
     }
-    if (best_t) { P->threads = best_t; P->smem_bytes = P->planes * best_t * (int)sizeof(uint32_t); P->arena = nullptr; }
+    if (best_t) { P->threads = best_t; P->smem_bytes = P->planes * best_t * (int)sizeof(plane_t); P->arena = nullptr; }
     else {
         P->threads = 128; P->smem_bytes = 0;
-        if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->arena, (size_t)P->planes * ctx->nwords * sizeof(uint32_t));
+        if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->arena, (size_t)P->planes * groups * sizeof(plane_t));
     }
     if (rc == QSB_OK && P->smem_bytes) {
-        cudaError_t e = cudaFuncSetAttribute(k_tab_exec, cudaFuncAttributeMaxDynamicSharedMemorySize, P->smem_bytes);
+        cudaError_t e = cudaFuncSetAttribute(exec_kernel(P->threads, P->arena != nullptr), cudaFuncAttributeMaxDynamicSharedMemorySize, P->smem_bytes);
         if (e != cudaSuccess) { qsb_set_error("cudaFuncSetAttribute(%d bytes) failed: %s", P->smem_bytes, cudaGetErrorString(e)); rc = QSB_ERR_CUDA; }
     }
     delete R;
     ctx->rec = nullptr;
-    if (rc != QSB_OK) { delete P; return rc; }
+    if (rc != QSB_OK) { if (P->h_ops) cudaFreeHost(P->h_ops); delete P; return rc; }
     *out = P;
     return QSB_OK;
 }
@@ -307,19 +417,44 @@ extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t dra
         QSB_LAUNCH_CHECK(ctx);
     }
     ExecArgs a;
-    a.ops = P->d_ops; a.nops = P->nops; a.obs = P->d_obs; a.arena = P->arena; a.valid = ctx->valid; a.W = (size_t)ctx->nwords;
+    a.ops = P->d_ops; a.nops = P->nops; a.obs = P->d_obs; a.arena = P->arena; a.valid = (const plane_t*)ctx->valid; a.W = (size_t)ctx->nwords * (32 / QSB_LANES);
     a.seed = ctx->seed; a.traj0 = (uint64_t)ctx->traj_offset + traj_shift; a.draw_base = draw_base;
-    unsigned blocks = (unsigned)((ctx->nwords + P->threads - 1) / P->threads);
+    a.bits = (const plane_t*)P->bits;
+    if (P->nspecs) {
+        QSB_PRE(ctx, "k_draw_bits");
+        k_draw_bits<<<(unsigned)((ctx->nwords * 32 + 255) / 256), 256, 0, ctx->stream>>>(P->d_specs, P->nspecs, P->bits, (size_t)ctx->nwords, a.seed, a.traj0, draw_base);
+        QSB_LAUNCH_CHECK(ctx);
+        // decision words: written once by the draw pass, read once by the executor
+        qsb_account(ctx, "k_draw_bits", (uint64_t)P->nslots * ctx->nwords * 4 + (uint64_t)P->nspecs * sizeof(DrawSpec));
+    }
+    unsigned blocks = (unsigned)((a.W + P->threads - 1) / P->threads);
     QSB_PRE(ctx, "k_tab_exec");
-    k_tab_exec<<<blocks, P->threads, P->smem_bytes, ctx->stream>>>(a);
+    exec_kernel(P->threads, P->arena != nullptr)<<<blocks, P->threads, P->smem_bytes, ctx->stream>>>(a);
     QSB_LAUNCH_CHECK(ctx);
+    // compulsory HBM traffic of the fused launch: the op list and the valid words once, the statistics rows and
+    // any per-trajectory observable rows written once -- the ensemble state itself never leaves the SM
+    qsb_account(ctx, "k_tab_exec", (uint64_t)P->nops * sizeof(TabOp) + (uint64_t)ctx->nwords * 4 + (uint64_t)P->nstats * 32 + (uint64_t)P->nslots * ctx->nwords * 4 +
+                                       P->per_traj_rows * (uint64_t)ctx->npad * 16);
+    ctx->ops += P->ops_per_run; ctx->draws += P->draws_per_run;
     return QSB_OK;
 }
 
-// info: {ops, arena planes, statistics rows, threads per block, shared bytes per block, 1 if the arena is in global memory}
-extern "C" int qsb_program_info(const qsb_program* P, int64_t info[6]) {
+// Re-sends the host op list to the device (asynchronous H2D on the context's stream): the op list is the
+// program's only host-side input, so an end-to-end timing that starts from host buffers includes this copy.
+extern "C" int qsb_program_upload(qsb_program* P, int64_t* bytes) {
+    if (!P) QSB_FAIL(QSB_ERR_BAD_ARG, "null program");
+    size_t b = (size_t)P->nops * sizeof(TabOp);
+    if (b) QSB_CUDA(cudaMemcpyAsync(P->d_ops, P->h_ops, b, cudaMemcpyHostToDevice, P->ctx->stream));
+    if (bytes) *bytes = (int64_t)b;
+    return QSB_OK;
+}
+
+// info: {ops, arena planes, statistics rows, threads per block, shared bytes per block, 1 if the arena is in global memory,
+//        register-state ops per run (all trajectories), draws per run}
+extern "C" int qsb_program_info(const qsb_program* P, int64_t info[8]) {
     if (!P || !info) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     info[0] = P->nops; info[1] = P->planes; info[2] = P->nstats; info[3] = P->threads; info[4] = P->smem_bytes; info[5] = P->arena ? 1 : 0;
+    info[6] = (int64_t)P->ops_per_run; info[7] = (int64_t)P->draws_per_run;
     return QSB_OK;
 }
 
@@ -327,7 +462,9 @@ extern "C" int qsb_program_free(qsb_program* P) {
     if (!P) return QSB_OK;
     qsb_ctx* ctx = P->ctx;
     qsb_dev_free(ctx, P->d_ops); qsb_dev_free(ctx, P->d_obs); qsb_dev_free(ctx, P->d_stats);
+    qsb_dev_free(ctx, P->d_specs); qsb_dev_free(ctx, P->bits);
     if (P->arena) qsb_dev_free(ctx, P->arena);
+    if (P->h_ops) cudaFreeHost(P->h_ops);
     delete P;
     return QSB_OK;
 }

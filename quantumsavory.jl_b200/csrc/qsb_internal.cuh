@@ -145,9 +145,11 @@ struct TabOp {
     double* stats;      // absolute device pointers captured at record time
     double* per_traj;
     int obs;            // index into the program's TabObsArgs table
+    int dslot;          // first decision-word slot of a stochastic op (filled at qsb_record_end)
 };
 int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes);
 void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes);
+void qsb_rec_shrink(qsb_ctx* ctx, int base, int old_planes, int new_planes);  // keep the head of a block, recycle its tail
 TabOp* qsb_rec_push(qsb_ctx* ctx, int type);           // zero-initialised op with all plane refs = -1
 int qsb_rec_push_obs(qsb_ctx* ctx, const void* tab_obs_args, size_t bytes);
 void qsb_rec_note_stats(qsb_ctx* ctx, double* p);

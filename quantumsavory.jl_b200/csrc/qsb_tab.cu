@@ -235,11 +235,11 @@ int qsbt_measure(qsb_state* st, int idx, int basis, uint64_t draw_id, qsb_mask* 
     int n = st->n;
     int tx = (basis == QSB_BASIS_X || basis == QSB_BASIS_Y), tz = (basis == QSB_BASIS_Z || basis == QSB_BASIS_Y);
     if (ctx->rec) {
-        int nb = qsb_rec_alloc_planes(ctx, qsb_tab_planes(n - 1));
+        // the qubit is removed IN PLACE (remove_qubit tolerates aliasing): the state keeps its base, the tail is recycled
         TabOp* o = qsb_rec_push(ctx, TOP_MEASURE); o->n = n; o->q[0] = idx; o->iv[0] = tx; o->iv[1] = tz; o->draw = draw_id;
-        o->s[0] = nb; o->s[1] = st->vbase; o->al[1] = st->valive; o->m[0] = outcome2->vplane; o->m[1] = was_random ? was_random->vplane : -1;
-        qsb_rec_free_planes(ctx, st->vbase, qsb_tab_planes(n));
-        st->vbase = nb; st->n = n - 1; st->bytes = qsb_state_bytes(ctx, QSB_TAB, n - 1);
+        o->s[0] = st->vbase; o->s[1] = st->vbase; o->al[1] = st->valive; o->m[0] = outcome2->vplane; o->m[1] = was_random ? was_random->vplane : -1;
+        qsb_rec_shrink(ctx, st->vbase, qsb_tab_planes(n), qsb_tab_planes(n - 1));
+        st->n = n - 1; st->bytes = qsb_state_bytes(ctx, QSB_TAB, n - 1);
         ctx->ops += ctx->ntraj; return QSB_OK;
     }
     void* nd;
@@ -263,10 +263,9 @@ int qsbt_ptrace(qsb_state* st, int idx) {
     qsb_ctx* ctx = st->ctx;
     int n = st->n;
     if (ctx->rec) {
-        int nb = qsb_rec_alloc_planes(ctx, qsb_tab_planes(n - 1));
-        TabOp* o = qsb_rec_push(ctx, TOP_PTRACE); o->n = n; o->q[0] = idx; o->s[0] = nb; o->s[1] = st->vbase;
-        qsb_rec_free_planes(ctx, st->vbase, qsb_tab_planes(n));
-        st->vbase = nb; st->n = n - 1; st->bytes = qsb_state_bytes(ctx, QSB_TAB, n - 1);
+        TabOp* o = qsb_rec_push(ctx, TOP_PTRACE); o->n = n; o->q[0] = idx; o->s[0] = st->vbase; o->s[1] = st->vbase;
+        qsb_rec_shrink(ctx, st->vbase, qsb_tab_planes(n), qsb_tab_planes(n - 1));
+        st->n = n - 1; st->bytes = qsb_state_bytes(ctx, QSB_TAB, n - 1);
         ctx->ops += ctx->ntraj; return QSB_OK;
     }
     void* nd;

@@ -14,6 +14,17 @@
 #define QSB_TAB_MAXN 32
 #endif
 #define MAXN QSB_TAB_MAXN
+// Storage type of one bit plane element: the number of trajectories ("lanes") one thread advances.  The per-op
+// kernels use 32-lane words; the fused executor (qsb_exec.cu) compiles this header with 8-lane bytes to get 4x
+// the threads out of the same ensemble.  Arithmetic is always done in 32-bit registers; QSB_FULL masks the lanes.
+#ifndef QSB_PLANE_T
+#define QSB_PLANE_T uint32_t
+#define QSB_CORE_NS tabcore32
+#endif
+namespace QSB_CORE_NS {
+typedef QSB_PLANE_T plane_t;
+#define QSB_LANES ((int)(8 * sizeof(plane_t)))
+#define QSB_FULL ((uint32_t)(plane_t)~(plane_t)0)
 
 QSB_HD uint32_t qsb_mulhi32(uint32_t a, uint32_t b) {
 #if defined(__CUDA_ARCH__)
@@ -38,9 +49,9 @@ QSB_HD double qsb_draw(uint64_t seed, uint64_t traj, uint64_t draw_id) {
 }
 
 struct TabView {
-    uint32_t* p; size_t W; size_t w; int n; int S;
-    QSB_HD uint32_t ld(int plane) const { return p[(size_t)plane * W + w]; }
-    QSB_HD void st(int plane, uint32_t v) const { p[(size_t)plane * W + w] = v; }
+    plane_t* p; size_t W; size_t w; int n; int S;
+    QSB_HD uint32_t ld(int plane) const { return (uint32_t)p[(size_t)plane * W + w]; }
+    QSB_HD void st(int plane, uint32_t v) const { p[(size_t)plane * W + w] = (plane_t)v; }
     QSB_HD int dx(int i, int c) const { return i * S + c; }
     QSB_HD int dz(int i, int c) const { return i * S + n + c; }
     QSB_HD int sx(int i, int c) const { return i * S + 2 * n + c; }
@@ -48,7 +59,7 @@ struct TabView {
     QSB_HD int sg(int i) const { return i * S + 4 * n; }
     QSB_HD int ac(int i) const { return i * S + 4 * n + 1; }
 };
-QSB_HD TabView make_view(uint32_t* p, size_t W, size_t w, int n) { TabView v; v.p = p; v.W = W; v.w = w; v.n = n; v.S = 4 * n + 2; return v; }
+QSB_HD TabView make_view(plane_t* p, size_t W, size_t w, int n) { TabView v; v.p = p; v.W = W; v.w = w; v.n = n; v.S = 4 * n + 2; return v; }
 
 
 // dst row (planes x0.., z0.., optional sign plane) <- src * dst on lanes m, src given in registers/local
@@ -129,7 +140,7 @@ QSB_HD uint32_t project_update(const TabView& v, uint32_t px, uint32_t pz, uint3
     int n = v.n;
     uint32_t pivD[MAXN];
     analyze(v, px, pz, A, pivD);
-    uint32_t found = A.found, det = ~found;
+    uint32_t found = A.found, det = ~found & QSB_FULL;
     uint32_t dsign = determined_sign(v, A, det);
     // logical-row pivots found on a D row: exchange D_i and S_i there (both are logical operators)
     for (int i = 0; i < n; ++i) {
@@ -163,7 +174,7 @@ QSB_HD uint32_t project_update(const TabView& v, uint32_t px, uint32_t pz, uint3
             uint32_t m = A.piv[i];
             if (m == 0) continue;
             for (int c = 0; c < n; ++c) {
-                uint32_t pxc = ((px >> c) & 1) ? 0xFFFFFFFFu : 0u, pzc = ((pz >> c) & 1) ? 0xFFFFFFFFu : 0u;
+                uint32_t pxc = ((px >> c) & 1) ? QSB_FULL : 0u, pzc = ((pz >> c) & 1) ? QSB_FULL : 0u;
                 v.st(v.dx(i, c), (v.ld(v.dx(i, c)) & ~m) | (pvx[c] & m));
                 v.st(v.dz(i, c), (v.ld(v.dz(i, c)) & ~m) | (pvz[c] & m));
                 v.st(v.sx(i, c), (v.ld(v.sx(i, c)) & ~m) | (pxc & m));
@@ -192,7 +203,7 @@ QSB_HD uint32_t project_update(const TabView& v, uint32_t px, uint32_t pz, uint3
             uint32_t m = pd[i];
             if (m == 0) continue;
             for (int c = 0; c < n; ++c) {
-                uint32_t pxc = ((px >> c) & 1) ? 0xFFFFFFFFu : 0u, pzc = ((pz >> c) & 1) ? 0xFFFFFFFFu : 0u;
+                uint32_t pxc = ((px >> c) & 1) ? QSB_FULL : 0u, pzc = ((pz >> c) & 1) ? QSB_FULL : 0u;
                 v.st(v.sx(i, c), (v.ld(v.sx(i, c)) & ~m) | (pxc & m));
                 v.st(v.sz(i, c), (v.ld(v.sz(i, c)) & ~m) | (pzc & m));
             }
@@ -214,14 +225,15 @@ QSB_HD void remove_qubit(const TabView& v, const TabView& o, int q, const Analys
     int last = n - 1;
     for (int i = 0; i < n - 1; ++i) {
         uint32_t m = A.piv[i];  // lanes whose pivot sits here take pair `last`
-        int cc = 0;
-        for (int c = 0; c < n; ++c) {
-            if (c == q) continue;
-            o.st(o.dx(i, cc), (v.ld(v.dx(i, c)) & ~m) | (v.ld(v.dx(last, c)) & m));
-            o.st(o.dz(i, cc), (v.ld(v.dz(i, c)) & ~m) | (v.ld(v.dz(last, c)) & m));
-            o.st(o.sx(i, cc), (v.ld(v.sx(i, c)) & ~m) | (v.ld(v.sx(last, c)) & m));
-            o.st(o.sz(i, cc), (v.ld(v.sz(i, c)) & ~m) | (v.ld(v.sz(last, c)) & m));
-            ++cc;
+        // plane order (pair, kind, column) ascending on both sides: every write lands at or below the plane
+        // just read, so `o` may alias `v` (in-place shrink inside a recorded program's arena)
+        for (int kind = 0; kind < 4; ++kind) {
+            int cc = 0;
+            for (int c = 0; c < n; ++c) {
+                if (c == q) continue;
+                o.st(i * o.S + kind * (n - 1) + cc, (v.ld(i * v.S + kind * n + c) & ~m) | (v.ld(last * v.S + kind * n + c) & m));
+                ++cc;
+            }
         }
         o.st(o.sg(i), (v.ld(v.sg(i)) & ~m) | (v.ld(v.sg(last)) & m));
         o.st(o.ac(i), (v.ld(v.ac(i)) & ~m) | (v.ld(v.ac(last)) & m));
@@ -231,7 +243,7 @@ QSB_HD void remove_qubit(const TabView& v, const TabView& o, int q, const Analys
 
 QSB_HD uint32_t lane_bits_ge_half(uint64_t seed, uint64_t traj0, size_t w, uint64_t draw_id) {
     uint32_t r = 0;
-    for (int l = 0; l < 32; ++l) if (qsb_draw(seed, traj0 + (uint64_t)(w * 32 + l), draw_id) >= 0.5) r |= 1u << l;
+    for (int l = 0; l < QSB_LANES; ++l) if (qsb_draw(seed, traj0 + (uint64_t)(w * QSB_LANES + l), draw_id) >= 0.5) r |= 1u << l;
     return r;
 }
 
@@ -239,21 +251,21 @@ QSB_HD uint32_t lane_bits_ge_half(uint64_t seed, uint64_t traj0, size_t w, uint6
 // ---------------------------------------------------------------------------------------------
 // per-word bodies of the kernels in qsb_tab.cu
 // ---------------------------------------------------------------------------------------------
-QSB_HD void tab_init_word(uint32_t* p, size_t W, size_t w, int n, int active) {
+QSB_HD void tab_init_word(plane_t* p, size_t W, size_t w, int n, int active) {
     TabView v = make_view(p, W, w, n);
     for (int i = 0; i < n; ++i) {
         for (int c = 0; c < n; ++c) {
-            v.st(v.dx(i, c), c == i ? 0xFFFFFFFFu : 0u); v.st(v.dz(i, c), 0u);
-            v.st(v.sx(i, c), 0u); v.st(v.sz(i, c), c == i ? 0xFFFFFFFFu : 0u);
+            v.st(v.dx(i, c), c == i ? QSB_FULL : 0u); v.st(v.dz(i, c), 0u);
+            v.st(v.sx(i, c), 0u); v.st(v.sz(i, c), c == i ? QSB_FULL : 0u);
         }
         v.st(v.sg(i), 0u);
-        v.st(v.ac(i), active ? 0xFFFFFFFFu : 0u);
+        v.st(v.ac(i), active ? QSB_FULL : 0u);
     }
 }
 
-QSB_HD void tab_tensor_word(uint32_t* out, const uint32_t* a, const uint32_t* b, size_t W, size_t w, int na, int nb) {
+QSB_HD void tab_tensor_word(plane_t* out, const plane_t* a, const plane_t* b, size_t W, size_t w, int na, int nb) {
     int n = na + nb;
-    TabView o = make_view(out, W, w, n), va = make_view((uint32_t*)a, W, w, na), vb = make_view((uint32_t*)b, W, w, nb);
+    TabView o = make_view(out, W, w, n), va = make_view((plane_t*)a, W, w, na), vb = make_view((plane_t*)b, W, w, nb);
     for (int i = 0; i < n; ++i) {
         bool fa = i < na;
         int j = fa ? i : i - na;
@@ -270,7 +282,7 @@ QSB_HD void tab_tensor_word(uint32_t* out, const uint32_t* a, const uint32_t* b,
 }
 
 struct TabGateArgs { int n, k, q[2]; uint8_t outmask[4]; uint32_t lut; };
-QSB_HD void tab_gate_word(uint32_t* p, size_t W, size_t w, const TabGateArgs& a, uint32_t m) {
+QSB_HD void tab_gate_word(plane_t* p, size_t W, size_t w, const TabGateArgs& a, uint32_t m) {
     if (m == 0) return;
     TabView v = make_view(p, W, w, a.n);
     int nb = 2 * a.k;
@@ -294,7 +306,7 @@ QSB_HD void tab_gate_word(uint32_t* p, size_t W, size_t w, const TabGateArgs& a,
                 uint32_t flip = 0;
                 for (int t = 0; t < (1 << nb); ++t) {
                     if (!((a.lut >> t) & 1)) continue;
-                    uint32_t term = 0xFFFFFFFFu;
+                    uint32_t term = QSB_FULL;
                     for (int j = 0; j < nb; ++j) term &= ((t >> j) & 1) ? in[j] : ~in[j];
                     flip |= term;
                 }
@@ -305,30 +317,46 @@ QSB_HD void tab_gate_word(uint32_t* p, size_t W, size_t w, const TabGateArgs& a,
 }
 
 struct TabNoiseArgs { int n, q, np; double cum[3]; int op[3]; /* 1 X, 2 Y, 3 Z */ };
-QSB_HD void tab_noise_word(uint32_t* p, size_t W, size_t w, size_t wg, const TabNoiseArgs& a, uint64_t seed, uint64_t traj0, uint64_t draw_id) {
-    uint32_t fx = 0, fz = 0;  // lanes receiving a Pauli with X / Z component
-    for (int l = 0; l < 32; ++l) {
-        double r = qsb_draw(seed, traj0 + (uint64_t)(wg * 32 + l), draw_id);
-        for (int i = 0; i < a.np; ++i) {
-            if (r > a.cum[i]) {
-                int P = a.op[i];
-                if (P == 1 || P == 2) fx |= 1u << l;
-                if (P == 3 || P == 2) fz |= 1u << l;
-                break;
-            }
+// which Pauli (bit 0: X component, bit 1: Z component) the draw r selects -- clifford/uptotime.jl:1-12
+QSB_HD uint32_t tab_noise_decide(const TabNoiseArgs& a, double r) {
+    for (int i = 0; i < a.np; ++i) {
+        if (r > a.cum[i]) {
+            int P = a.op[i];
+            return ((P == 1 || P == 2) ? 1u : 0u) | ((P == 3 || P == 2) ? 2u : 0u);
         }
     }
+    return 0u;
+}
+// fx / fz: lanes receiving a Pauli with X / Z component
+QSB_HD void tab_noise_apply(plane_t* p, size_t W, size_t w, int n, int q, uint32_t fx, uint32_t fz) {
     if ((fx | fz) == 0) return;
-    TabView v = make_view(p, W, w, a.n);
-    for (int i = 0; i < a.n; ++i) {  // sign of S_i flips where it anticommutes with the applied Pauli
-        uint32_t flip = (v.ld(v.sx(i, a.q)) & fz) ^ (v.ld(v.sz(i, a.q)) & fx);
+    TabView v = make_view(p, W, w, n);
+    for (int i = 0; i < n; ++i) {  // sign of S_i flips where it anticommutes with the applied Pauli
+        uint32_t flip = (v.ld(v.sx(i, q)) & fz) ^ (v.ld(v.sz(i, q)) & fx);
         if (flip) v.st(v.sg(i), v.ld(v.sg(i)) ^ flip);
     }
+}
+QSB_HD void tab_noise_word(plane_t* p, size_t W, size_t w, size_t wg, const TabNoiseArgs& a, uint64_t seed, uint64_t traj0, uint64_t draw_id) {
+    uint32_t fx = 0, fz = 0;
+    for (int l = 0; l < QSB_LANES; ++l) {
+        uint32_t d = tab_noise_decide(a, qsb_draw(seed, traj0 + (uint64_t)(wg * QSB_LANES + l), draw_id));
+        fx |= (d & 1u) << l; fz |= (d >> 1) << l;
+    }
+    tab_noise_apply(p, W, w, a.n, a.q, fx, fz);
 }
 
 // project_traceout! on a tableau (a9): projectremoverand!(state, projectX!/Y!/Z!, idx).
 // returns the outcome word (bit = 1 for outcome 2); *rnd = lanes whose outcome consumed the draw.
-QSB_HD uint32_t tab_measure_word(uint32_t* in, uint32_t* out, size_t W, size_t w, size_t wg, int n, int q, int tx, int tz,
+// rbits: per-lane random eigenvalue bit (draw >= 0.5), used only on the lanes where the outcome is random
+QSB_HD uint32_t tab_measure_bits(plane_t* in, plane_t* out, size_t W, size_t w, int n, int q, int tx, int tz, uint32_t rbits, uint32_t* rnd) {
+    TabView v = make_view(in, W, w, n), o = make_view(out, W, w, n - 1);
+    Analysis A;
+    uint32_t outcome = project_update(v, (uint32_t)tx << q, (uint32_t)tz << q, rbits, true, A);
+    *rnd = A.found;
+    if (n > 1) remove_qubit(v, o, q, A, outcome, 0u);
+    return outcome;
+}
+QSB_HD uint32_t tab_measure_word(plane_t* in, plane_t* out, size_t W, size_t w, size_t wg, int n, int q, int tx, int tz,
                                  uint64_t seed, uint64_t traj0, uint64_t draw_id, uint32_t* rnd) {
     TabView v = make_view(in, W, w, n), o = make_view(out, W, w, n - 1);
     Analysis A;
@@ -340,7 +368,7 @@ QSB_HD uint32_t tab_measure_word(uint32_t* in, uint32_t* out, size_t W, size_t w
 }
 
 // traceout! on a tableau (a10): the group of ptrace_q(rho) is { g in G : g|_q = I }.
-QSB_HD void tab_ptrace_word(uint32_t* in, uint32_t* out, size_t W, size_t w, int n, int q) {
+QSB_HD void tab_ptrace_word(plane_t* in, plane_t* out, size_t W, size_t w, int n, int q) {
     TabView v = make_view(in, W, w, n), o = make_view(out, W, w, n - 1);
     Analysis A;
     uint32_t outcome = project_update(v, 0u, 1u << q, 0u, true, A);  // Z_q; the sign is forgotten on random lanes
@@ -374,27 +402,31 @@ QSB_HD void tab_ptrace_word(uint32_t* in, uint32_t* out, size_t W, size_t w, int
 }
 
 // force a (multi-qubit) Pauli with a given sign into the group: used to build a state from generators
-QSB_HD void tab_force_word(uint32_t* p, size_t W, size_t w, int n, uint32_t px, uint32_t pz, int sign) {
+QSB_HD void tab_force_word(plane_t* p, size_t W, size_t w, int n, uint32_t px, uint32_t pz, int sign) {
     TabView v = make_view(p, W, w, n);
     Analysis A;
-    project_update(v, px, pz, sign ? 0xFFFFFFFFu : 0u, false, A);
+    project_update(v, px, pz, sign ? QSB_FULL : 0u, false, A);
 }
 
 struct TabObsArgs { int n, k, nelem; uint32_t px[64], pz[64]; uint8_t sign[64]; };
 // Each element h of the observable's Pauli group contributes <h> in {-1,0,+1}; a single Pauli is the
 // 1-element case.  value = sum_h <h> / nelem (for a projector the signs are a character of the subgroup
 // with non-zero expectation, so the sum is |H| or 0).  Bit-sliced tallies of the +1 and -1 terms.
-QSB_HD void tab_expect_word(uint32_t* p, size_t W, size_t w, const TabObsArgs& a, uint32_t* cnt, uint32_t* cntm) {
-    TabView v = make_view(p, W, w, a.n);
+QSB_HD void tab_expect_word_n(plane_t* p, size_t W, size_t w, int n, const TabObsArgs& a, uint32_t* cnt, uint32_t* cntm);
+QSB_HD void tab_expect_word(plane_t* p, size_t W, size_t w, const TabObsArgs& a, uint32_t* cnt, uint32_t* cntm) {
+    tab_expect_word_n(p, W, w, a.n, a, cnt, cntm);
+}
+QSB_HD void tab_expect_word_n(plane_t* p, size_t W, size_t w, int n, const TabObsArgs& a, uint32_t* cnt, uint32_t* cntm) {
+    TabView v = make_view(p, W, w, n);
     for (int b = 0; b < 8; ++b) { cnt[b] = 0; cntm[b] = 0; }
     Analysis A;
     uint32_t pivD[MAXN];
     for (int e = 0; e < a.nelem; ++e) {
         uint32_t nonzero, neg;
-        if ((a.px[e] | a.pz[e]) == 0) { nonzero = 0xFFFFFFFFu; neg = a.sign[e] ? 0xFFFFFFFFu : 0u; }
+        if ((a.px[e] | a.pz[e]) == 0) { nonzero = QSB_FULL; neg = a.sign[e] ? QSB_FULL : 0u; }
         else {
             analyze(v, a.px[e], a.pz[e], A, pivD);
-            nonzero = ~A.found;
+            nonzero = ~A.found & QSB_FULL;
             neg = determined_sign(v, A, nonzero) ^ (a.sign[e] ? nonzero : 0u);
         }
         uint32_t carry = nonzero & ~neg;
@@ -403,3 +435,5 @@ QSB_HD void tab_expect_word(uint32_t* p, size_t W, size_t w, const TabObsArgs& a
         for (int b = 0; b < 8 && carry; ++b) { uint32_t t = cntm[b] & carry; cntm[b] ^= carry; carry = t; }
     }
 }
+}  // namespace QSB_CORE_NS
+using namespace QSB_CORE_NS;
