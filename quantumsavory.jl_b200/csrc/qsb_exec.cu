@@ -37,6 +37,7 @@ struct DrawSpec {
 struct qsb_program {
     qsb_ctx* ctx;
     DrawSpec* d_specs; int nspecs, nslots;
+    uint8_t* d_aux; int naux, nfolded;   // constant tables of folded ops
     uint32_t* bits;        // [nslots][nwords] decision words written by k_draw_bits, read by k_tab_exec
     TabOp* d_ops; int nops;
     TabObsArgs* d_obs; int nobs;
@@ -109,6 +110,7 @@ int qsb_rec_push_obs(qsb_ctx* ctx, const void* a, size_t bytes) {
 struct ExecArgs {
     const TabOp* ops; int nops;
     const TabObsArgs* obs;
+    const uint8_t* aux;
     plane_t* arena;           // nullptr -> shared-memory tile
     const plane_t* bits;      // decision bits of every stochastic op, [slot][W] (the draw pass's words seen lane-group wise)
     const plane_t* valid;
@@ -212,12 +214,27 @@ __global__ void __launch_bounds__(T ? T : 128) k_tab_exec(ExecArgs a) {
                 PL(op.al[0])[w] = al;
             }
             break;
+        case TOP_SELECT_CONST:
+            if (on) {
+                uint32_t m[5];
+                const plane_t* d = a.bits + (size_t)op.dslot * a.W + wg;
+                const uint32_t b0 = d[0], b1 = d[a.W], b2 = d[2 * a.W];
+                for (int j = 0; j < 5; ++j) m[j] = ((j & 1) ? b0 : ~b0) & ((j & 2) ? b1 : ~b1) & ((j & 4) ? b2 : ~b2);
+                const uint8_t* tab = a.aux + op.obs;
+                const int planes = op.n * (4 * op.n + 2);
+                for (int p = 0; p < planes; ++p) {
+                    const uint32_t c = tab[p];
+                    uint32_t v = 0;
+                    for (int j = 0; j < 5; ++j) v |= ((c >> j) & 1) ? m[j] : 0u;
+                    PL(op.s[0] + p)[w] = (plane_t)v;
+                }
+                PL(op.al[0])[w] = (plane_t)validw;
+            }
+            break;
         case TOP_GATE:
             if (on) {
-                TabGateArgs g; g.n = op.n; g.k = op.k; g.q[0] = op.q[0]; g.q[1] = op.q[1]; g.lut = op.lut;
-                for (int j = 0; j < 4; ++j) g.outmask[j] = op.outmask[j];
                 const uint32_t gm = op.m[0] >= 0 ? (uint32_t)PL(op.m[0])[w] : QSB_FULL;
-                N_SWITCH(op.n, g.n = N; tab_gate_word(PL(op.s[0]), W, w, g, gm))
+                N_SWITCH(op.n, tab_gate_anf(PL(op.s[0]), W, w, N, op.k, op.q[0], op.q[1], op.outmask, op.u[0], gm))
             }
             break;
         case TOP_NOISE:
@@ -244,29 +261,40 @@ __global__ void __launch_bounds__(T ? T : 128) k_tab_exec(ExecArgs a) {
             if (on) { N_SWITCH(op.n, tab_force_word(PL(op.s[0]), W, w, N, op.u[0], op.u[1], op.iv[0])) }
             break;
         case TOP_EXPECT: {
-            double s_alive = 0, s_v = 0, s_v2 = 0;
+            // integer tallies (exact, order independent): alive lanes, sum of (plus - minus), sum of its square
+            int n_alive = 0, num = 0, num2 = 0;
+            int nelem = 1;
             if (on) {
                 const TabObsArgs& o = a.obs[op.obs];
+                nelem = o.nelem;
                 uint32_t cnt[8], cntm[8];
                 N_SWITCH(op.n, tab_expect_word_n(PL(op.s[0]), W, w, N, o, cnt, cntm))
-                uint32_t al = PL(op.al[0])[w];
-                double inv = 1.0 / (double)o.nelem;
-                for (int l = 0; l < QSB_LANES; ++l) {
-                    int plus = 0, minus = 0;
-                    for (int b = 0; b < 8; ++b) { plus |= ((cnt[b] >> l) & 1) << b; minus |= ((cntm[b] >> l) & 1) << b; }
-                    bool lane = (al >> l) & 1u;
-                    double val = lane ? (double)(plus - minus) * inv : 0.0;
-                    if (op.per_traj) { size_t t = wg * QSB_LANES + l; op.per_traj[2 * t] = val; op.per_traj[2 * t + 1] = 0.0; }
-                    if (lane) { s_alive += 1.0; s_v += val; s_v2 += val * val; }
+                const uint32_t al = PL(op.al[0])[w];
+                n_alive = __popc(al);
+                if (nelem == 1 && !op.per_traj) {   // a single Pauli: each lane holds -1, 0 or +1
+                    num = __popc(cnt[0] & al) - __popc(cntm[0] & al);
+                    num2 = __popc((cnt[0] | cntm[0]) & al);
+                } else {
+                    const double inv = 1.0 / (double)nelem;
+                    for (int l = 0; l < QSB_LANES; ++l) {
+                        int plus = 0, minus = 0;
+                        for (int b = 0; b < 8; ++b) { plus |= ((cnt[b] >> l) & 1) << b; minus |= ((cntm[b] >> l) & 1) << b; }
+                        const bool lane = (al >> l) & 1u;
+                        const int d = lane ? plus - minus : 0;
+                        if (op.per_traj) { size_t t = wg * QSB_LANES + l; op.per_traj[2 * t] = (double)d * inv; op.per_traj[2 * t + 1] = 0.0; }
+                        num += d; num2 += d * d;
+                    }
                 }
             }
             if (op.stats) {  // whole warps reach this point together (the op list is uniform)
-                for (int o = 16; o; o >>= 1) {
-                    s_alive += __shfl_xor_sync(0xffffffffu, s_alive, o);
-                    s_v += __shfl_xor_sync(0xffffffffu, s_v, o);
-                    s_v2 += __shfl_xor_sync(0xffffffffu, s_v2, o);
+                n_alive = __reduce_add_sync(0xffffffffu, n_alive);
+                num = __reduce_add_sync(0xffffffffu, num);
+                num2 = __reduce_add_sync(0xffffffffu, num2);
+                nelem = __reduce_max_sync(0xffffffffu, nelem);
+                if ((threadIdx.x & 31) == 0 && n_alive) {
+                    const double inv = 1.0 / (double)nelem;   // nelem = 2^k: the scaled tallies are exact
+                    atomicAdd(&op.stats[0], (double)n_alive); atomicAdd(&op.stats[1], (double)num * inv); atomicAdd(&op.stats[2], (double)num2 * inv * inv);
                 }
-                if ((threadIdx.x & 31) == 0 && s_alive != 0.0) { atomicAdd(&op.stats[0], s_alive); atomicAdd(&op.stats[1], s_v); atomicAdd(&op.stats[2], s_v2); }
             }
             break;
         }
@@ -339,14 +367,62 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     ctx->ops = R->ops0; ctx->draws = R->draws0;  // counted per qsb_program_run instead
     for (auto& o : R->ops) if (o.per_traj) P->per_traj_rows++;
     int rc = QSB_OK;
+    // Constant folding: a mixture's components are built by INIT (+FORCE...) ops whose result is the same on every
+    // lane.  Evaluate those on the host (the tableau core is host-callable), drop them, and let the SELECT pick each
+    // plane from a per-plane table of "which components have this bit set" instead of reading component tableaux.
+    std::vector<uint8_t> aux;
+    {
+        struct Pend { std::vector<int> ops; int alive, n; };
+        std::map<int, Pend> pend;   // state base plane -> the ops that built it, untouched by anything else so far
+        std::vector<plane_t> h((size_t)P->planes + 8, 0);
+        for (int i = 0; i < (int)R->ops.size(); ++i) {
+            TabOp& o = R->ops[i];
+            if (o.type == TOP_INIT) { pend[o.s[0]] = Pend{{i}, o.al[0], o.n}; continue; }
+            if (o.type == TOP_FORCE) { auto it = pend.find(o.s[0]); if (it != pend.end()) it->second.ops.push_back(i); continue; }
+            bool fold = o.type == TOP_SELECT && qsb_tab_planes(o.n) <= 4096;
+            if (fold) for (int j = 0; j < o.n2; ++j) { auto it = pend.find(o.s[1 + j]); if (it == pend.end() || it->second.alive != o.al[1 + j] || it->second.n != o.n) fold = false; }
+            if (fold) {
+                const int planes = qsb_tab_planes(o.n);
+                std::vector<uint8_t> tab(planes, 0);
+                for (int j = 0; j < o.n2 && fold; ++j) {
+                    for (int k : pend[o.s[1 + j]].ops) {
+                        const TabOp& c = R->ops[k];
+                        if (c.type == TOP_INIT) tab_init_word(h.data() + c.s[0], 1, 0, c.n, c.iv[0]);
+                        else tab_force_word(h.data() + c.s[0], 1, 0, c.n, c.u[0], c.u[1], c.iv[0]);
+                    }
+                    for (int p = 0; p < planes; ++p) {
+                        plane_t v = h[(size_t)o.s[1 + j] + p];
+                        if (v == (plane_t)QSB_FULL) tab[p] |= 1u << j; else if (v != 0) fold = false;   // not lane-uniform: keep the ops
+                    }
+                }
+                if (fold) {
+                    for (int j = 0; j < o.n2; ++j) { for (int k : pend[o.s[1 + j]].ops) R->ops[k].type = TOP_NOP; pend.erase(o.s[1 + j]); }
+                    o.type = TOP_SELECT_CONST; o.obs = (int)aux.size();
+                    aux.insert(aux.end(), tab.begin(), tab.end());
+                    P->nfolded++;
+                }
+            }
+            // any other use of a pending state (or of its alive plane) makes it a real state again
+            for (auto it = pend.begin(); it != pend.end();) {
+                bool used = false;
+                for (int k = 0; k < 6; ++k) used |= (o.s[k] == it->first) || (o.al[k] == it->second.alive);
+                it = used ? pend.erase(it) : std::next(it);
+            }
+        }
+        // drop the NOPs
+        std::vector<TabOp> kept;
+        for (auto& o : R->ops) if (o.type != TOP_NOP) kept.push_back(o);
+        R->ops.swap(kept);
+        P->nops = (int)R->ops.size(); P->naux = (int)aux.size();
+    }
     // stochastic ops -> draw specs + decision-word slots (noise: fx,fz; mixture: 3 index planes; others: 1)
     std::vector<DrawSpec> specs;
     for (auto& o : R->ops) {
-        int need = o.type == TOP_NOISE ? 2 : o.type == TOP_SELECT ? 3 : (o.type == TOP_MEASURE || o.type == TOP_MASK_RANDOM) ? 1 : 0;
+        int need = o.type == TOP_NOISE ? 2 : (o.type == TOP_SELECT || o.type == TOP_SELECT_CONST) ? 3 : (o.type == TOP_MEASURE || o.type == TOP_MASK_RANDOM) ? 1 : 0;
         if (!need) continue;
         DrawSpec d; memset(&d, 0, sizeof(d));
-        d.draw = o.draw; d.type = o.type; d.slot = P->nslots;
-        d.np = o.type == TOP_NOISE ? o.k : o.type == TOP_SELECT ? o.n2 : 1;
+        d.draw = o.draw; d.type = o.type == TOP_SELECT_CONST ? (int)TOP_SELECT : o.type; d.slot = P->nslots;
+        d.np = o.type == TOP_NOISE ? o.k : d.type == TOP_SELECT ? o.n2 : 1;
         for (int j = 0; j < 5; ++j) d.cum[j] = o.f[j];
         for (int j = 0; j < 3; ++j) d.op[j] = o.iv[j];
         o.dslot = P->nslots; P->nslots += need;
@@ -369,6 +445,7 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     up((void**)&P->d_obs, R->obs.data(), R->obs.size() * sizeof(TabObsArgs));
     up((void**)&P->d_stats, R->stats_ptrs.data(), R->stats_ptrs.size() * sizeof(double*));
     up((void**)&P->d_specs, specs.data(), specs.size() * sizeof(DrawSpec));
+    up((void**)&P->d_aux, aux.data(), aux.size());
     if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->bits, (size_t)(P->nslots ? P->nslots : 1) * ctx->nwords * sizeof(uint32_t));
     if (rc == QSB_OK) { cudaError_t e = cudaStreamSynchronize(ctx->stream); if (e != cudaSuccess) rc = QSB_ERR_CUDA; }  // host vectors die below
     // launch shape: the largest block whose [planes][threads] tile fits, preferring a single wave
@@ -417,7 +494,7 @@ extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t dra
         QSB_LAUNCH_CHECK(ctx);
     }
     ExecArgs a;
-    a.ops = P->d_ops; a.nops = P->nops; a.obs = P->d_obs; a.arena = P->arena; a.valid = (const plane_t*)ctx->valid; a.W = (size_t)ctx->nwords * (32 / QSB_LANES);
+    a.ops = P->d_ops; a.nops = P->nops; a.obs = P->d_obs; a.aux = P->d_aux; a.arena = P->arena; a.valid = (const plane_t*)ctx->valid; a.W = (size_t)ctx->nwords * (32 / QSB_LANES);
     a.seed = ctx->seed; a.traj0 = (uint64_t)ctx->traj_offset + traj_shift; a.draw_base = draw_base;
     a.bits = (const plane_t*)P->bits;
     if (P->nspecs) {
@@ -462,7 +539,7 @@ extern "C" int qsb_program_free(qsb_program* P) {
     if (!P) return QSB_OK;
     qsb_ctx* ctx = P->ctx;
     qsb_dev_free(ctx, P->d_ops); qsb_dev_free(ctx, P->d_obs); qsb_dev_free(ctx, P->d_stats);
-    qsb_dev_free(ctx, P->d_specs); qsb_dev_free(ctx, P->bits);
+    qsb_dev_free(ctx, P->d_specs); qsb_dev_free(ctx, P->bits); qsb_dev_free(ctx, P->d_aux);
     if (P->arena) qsb_dev_free(ctx, P->arena);
     if (P->h_ops) cudaFreeHost(P->h_ops);
     delete P;

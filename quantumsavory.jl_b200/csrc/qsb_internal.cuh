@@ -130,7 +130,8 @@ int qsbt_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* 
 
 // ---- recorded programs (qsb_exec.cu): tableau op lists executed by ONE fused launch ----------------
 enum { TOP_INIT, TOP_TENSOR, TOP_SELECT, TOP_COPY, TOP_GATE, TOP_NOISE, TOP_MEASURE, TOP_PTRACE, TOP_FORCE, TOP_EXPECT,
-       TOP_MASK_FILL, TOP_MASK_LOGIC, TOP_MASK_RANDOM, TOP_KILL, TOP_ALIVE_COPY };
+       TOP_MASK_FILL, TOP_MASK_LOGIC, TOP_MASK_RANDOM, TOP_KILL, TOP_ALIVE_COPY,
+       TOP_NOP, TOP_SELECT_CONST /* produced by constant folding at qsb_record_end */ };
 struct TabOp {
     int type, n, n2, k;
     int s[6];       // state base planes (s[0] is the destination where there is one)

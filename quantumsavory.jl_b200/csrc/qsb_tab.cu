@@ -148,9 +148,10 @@ int qsbt_apply(qsb_state* st, const int* idx, int k, const uint8_t* table, const
     }
     if (table[0] != 0) QSB_FAIL(QSB_ERR_BAD_ARG, "conjugation table maps the identity to a non-identity");
     for (int b = 0; b < nb; ++b) for (int j = 0; j < nb; ++j) if ((cols[j] >> b) & 1) a.outmask[b] |= 1 << j;
+    a.anf = tab_lut_to_anf(a.lut, nb);
     if (mask) QSB_TRY(qsb_handle_ok(ctx, mask->vplane >= 0, mask->gen));
     if (ctx->rec) {
-        TabOp* o = qsb_rec_push(ctx, TOP_GATE); o->n = a.n; o->k = a.k; o->q[0] = a.q[0]; o->q[1] = a.q[1]; o->lut = a.lut;
+        TabOp* o = qsb_rec_push(ctx, TOP_GATE); o->n = a.n; o->k = a.k; o->q[0] = a.q[0]; o->q[1] = a.q[1]; o->lut = a.lut; o->u[0] = a.anf;
         for (int j = 0; j < 4; ++j) o->outmask[j] = a.outmask[j];
         o->s[0] = st->vbase; o->m[0] = mask ? mask->vplane : -1;
         ctx->ops += ctx->ntraj; return QSB_OK;

@@ -281,39 +281,69 @@ QSB_HD void tab_tensor_word(plane_t* out, const plane_t* a, const plane_t* b, si
     }
 }
 
-struct TabGateArgs { int n, k, q[2]; uint8_t outmask[4]; uint32_t lut; };
-QSB_HD void tab_gate_word(plane_t* p, size_t W, size_t w, const TabGateArgs& a, uint32_t m) {
-    if (m == 0) return;
-    TabView v = make_view(p, W, w, a.n);
-    int nb = 2 * a.k;
-    for (int i = 0; i < a.n; ++i) {
+struct TabGateArgs { int n, k, q[2]; uint8_t outmask[4]; uint32_t lut, anf; /* anf = tab_lut_to_anf(lut, 2k), filled by the host */ };
+// Sign truth table (bit t of lut: the image of the Pauli with input bits t picks up a minus) -> algebraic normal
+// form: bit t of the result = monomial AND_{j in t} in[j] is present.  Standard gates have 0-3 monomials
+// (Paulis: linear; CNOT: x_c z_t x_t + x_c z_t z_c + x_c z_t), so the kernels XOR a few ANDs instead of
+// OR-ing up to 16 minterms.
+QSB_HD uint32_t tab_lut_to_anf(uint32_t lut, int nb) {
+    uint32_t f = lut;
+    for (int j = 0; j < nb; ++j)
+        for (int t = 0; t < (1 << nb); ++t)
+            if ((t >> j) & 1) f ^= ((f >> (t ^ (1 << j))) & 1u) << t;
+    return f;
+}
+QSB_HD int qsb_ctz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+}
+// conjugation of every row by a K-qubit Clifford gate on the lanes m: the (x,z) bits of the target qubits go
+// through the GF(2)-linear map `outmask` (only outputs that differ from their input are recomputed and stored),
+// stabilizer signs flip where the ANF of the sign table evaluates to 1.
+template <int K>
+QSB_HD void tab_gate_rows(const TabView& v, int q0, int q1, const uint8_t* om, uint32_t anf, uint32_t m) {
+    constexpr int NB = 2 * K;
+    const int n = v.n;
+    uint32_t chg = 0;
+    for (int b = 0; b < NB; ++b) if (om[b] != (1u << b)) chg |= 1u << b;
+    for (int i = 0; i < n; ++i) {
         for (int half = 0; half < 2; ++half) {
-            int px[2], pz[2];
-            for (int j = 0; j < a.k; ++j) { px[j] = half ? v.sx(i, a.q[j]) : v.dx(i, a.q[j]); pz[j] = half ? v.sz(i, a.q[j]) : v.dz(i, a.q[j]); }
-            uint32_t in[4] = {0, 0, 0, 0};
-            for (int j = 0; j < a.k; ++j) { in[2 * j] = v.ld(px[j]); in[2 * j + 1] = v.ld(pz[j]); }
-            uint32_t outv[4];
-            for (int b = 0; b < nb; ++b) {
+            if (!half && !chg) continue;                      // Pauli gates touch signs only
+            const int xb = i * v.S + half * 2 * n, zb = xb + n;
+            uint32_t in[NB];
+            in[0] = v.ld(xb + q0); in[1] = v.ld(zb + q0);
+            if (K == 2) { in[NB - 2] = v.ld(xb + q1); in[NB - 1] = v.ld(zb + q1); }
+            for (int b = 0; b < NB; ++b) {
+                if (!((chg >> b) & 1)) continue;
                 uint32_t o = 0;
-                for (int j = 0; j < nb; ++j) if ((a.outmask[b] >> j) & 1) o ^= in[j];
-                outv[b] = o;
+                for (int j = 0; j < NB; ++j) o ^= ((om[b] >> j) & 1) ? in[j] : 0u;
+                v.st(((b & 1) ? zb : xb) + ((b >> 1) ? q1 : q0), in[b] ^ ((in[b] ^ o) & m));
             }
-            for (int j = 0; j < a.k; ++j) {
-                v.st(px[j], (in[2 * j] & ~m) | (outv[2 * j] & m));
-                v.st(pz[j], (in[2 * j + 1] & ~m) | (outv[2 * j + 1] & m));
-            }
-            if (half && a.lut) {
+            if (half && anf) {
                 uint32_t flip = 0;
-                for (int t = 0; t < (1 << nb); ++t) {
-                    if (!((a.lut >> t) & 1)) continue;
+                for (uint32_t t = anf; t; t &= t - 1) {
+                    const int k = qsb_ctz32(t);
                     uint32_t term = QSB_FULL;
-                    for (int j = 0; j < nb; ++j) term &= ((t >> j) & 1) ? in[j] : ~in[j];
-                    flip |= term;
+                    for (int j = 0; j < NB; ++j) term &= ((k >> j) & 1) ? in[j] : QSB_FULL;
+                    flip ^= term;
                 }
-                v.st(v.sg(i), v.ld(v.sg(i)) ^ (flip & m));
+                flip &= m;
+                if (flip) v.st(v.sg(i), v.ld(v.sg(i)) ^ flip);
             }
         }
     }
+}
+QSB_HD void tab_gate_anf(plane_t* p, size_t W, size_t w, int n, int k, int q0, int q1, const uint8_t* om, uint32_t anf, uint32_t m) {
+    if (m == 0) return;
+    TabView v = make_view(p, W, w, n);
+    if (k == 1) tab_gate_rows<1>(v, q0, q0, om, anf, m);
+    else tab_gate_rows<2>(v, q0, q1, om, anf, m);
+}
+QSB_HD void tab_gate_word(plane_t* p, size_t W, size_t w, const TabGateArgs& a, uint32_t m) {
+    tab_gate_anf(p, W, w, a.n, a.k, a.q[0], a.q[1], a.outmask, a.anf, m);
 }
 
 struct TabNoiseArgs { int n, q, np; double cum[3]; int op[3]; /* 1 X, 2 Y, 3 Z */ };

@@ -38,6 +38,7 @@ int et_gate(ETab* t, const int* idx, int k, const uint8_t* table, const uint32_t
         if ((table[x] >> nb) & 1) a.lut |= 1u << x;
     }
     for (int b = 0; b < nb; ++b) for (int j = 0; j < nb; ++j) if ((cols[j] >> b) & 1) a.outmask[b] |= 1 << j;
+    a.anf = tab_lut_to_anf(a.lut, nb);
     for (size_t w = 0; w < t->W; ++w) tab_gate_word(t->p.data(), t->W, w, a, mask ? mask[w] : 0xFFFFFFFFu);
     return 0;
 }
