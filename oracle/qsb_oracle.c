@@ -64,12 +64,15 @@ static void philox4x32_10(const uint32_t ctr_in[4], const uint32_t key_in[2], ui
 
 void qso_philox(const uint32_t* ctr, const uint32_t* key, uint32_t* out) { philox4x32_10(ctr, key, out); }
 
+/* The injected draw: one Philox block (counter = trajectory, draw_id / 2) carries two 53-bit uniforms,
+ * words (0,1) for even draw ids and (2,3) for odd ones. */
 double qso_draw(uint64_t seed, uint64_t traj, uint64_t draw_id) {
-    uint32_t ctr[4] = {(uint32_t)traj, (uint32_t)(traj >> 32), (uint32_t)draw_id, (uint32_t)(draw_id >> 32)};
+    uint64_t block = draw_id >> 1;
+    uint32_t ctr[4] = {(uint32_t)traj, (uint32_t)(traj >> 32), (uint32_t)block, (uint32_t)(block >> 32)};
     uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     uint32_t o[4];
     philox4x32_10(ctr, key, o);
-    uint64_t bits = ((uint64_t)o[1] << 32) | o[0];
+    uint64_t bits = (draw_id & 1) ? (((uint64_t)o[3] << 32) | o[2]) : (((uint64_t)o[1] << 32) | o[0]);
     return (double)(bits >> 11) * (1.0 / 9007199254740992.0);
 }
 

@@ -10,12 +10,12 @@
 // Lanes per thread: this translation unit compiles the tableau core with 8-lane BYTE planes (QSB_PLANE_T), so an
 // ensemble of N trajectories runs on N/8 threads instead of N/32 -- the bit logic is latency bound (dependent
 // shared-memory round trips), and 10^6 trajectories are only 977 warps of 32-lane words on 148 SMs.
-#define QSB_PLANE_T uint8_t
-#define QSB_CORE_NS tabcore8
+#include <limits.h>
+#include <math.h>
+#include <algorithm>
 #include <map>
 
-#include "qsb_internal.cuh"
-#include "qsb_tab_core.cuh"
+#include "qsb_exec_kernel.cuh"
 
 struct qsb_recorder {
     std::vector<TabOp> ops;
@@ -24,34 +24,43 @@ struct qsb_recorder {
     int next_plane = 0, high = 0;
     std::multimap<int, int> free_blocks;  // size -> base
     uint64_t ops0 = 0, draws0 = 0;        // context counters at qsb_record_begin (recording itself executes nothing)
+    // lifetime log of every plane block, for the offline re-packing of the arena at qsb_record_end:
+    // live for ops [t0, t1); sizes.back().second planes from op sizes.back().first on (in-place shrinks)
+    struct Blk { int base, t0, t1; std::vector<std::pair<int, int>> sizes; int nbase; bool used; };
+    std::vector<Blk> blks;
+    std::map<int, int> live;              // online base -> index into blks
+    int now() const { return (int)ops.size(); }
 };
 
 // one stochastic op of the program as the draw pass sees it
 struct DrawSpec {
     uint64_t draw;
     int type, np, slot, pad;   // type: TOP_NOISE / TOP_SELECT / TOP_MEASURE / TOP_MASK_RANDOM
-    double cum[5];
-    int op[3];
+    // the comparisons of the per-op kernels (u = k / 2^53 against a double c) restated EXACTLY on the 53-bit integer k:
+    //   u > c  <=>  k > floor(c * 2^53)        u < c  <=>  k < ceil(c * 2^53)        (c * 2^53 is exact in a double)
+    uint64_t thr[5];
+    uint64_t thr_any;          // noise: the lowest threshold -- k <= thr_any on every lane means "no error anywhere in this word"
+    uint8_t code[4];           // noise: 2-bit decision (bit 0: X component, bit 1: Z component) of branch j
+    int pad2;
 };
+#define QSB_DRAW_CHUNK 64      // specs staged per shared-memory refill of the draw pass
 
 struct qsb_program {
     qsb_ctx* ctx;
-    DrawSpec* d_specs; int nspecs, nslots;
+    DrawSpec* d_specs; int nspecs, nslots, slot_stride;
     uint8_t* d_aux; int naux, nfolded;   // constant tables of folded ops
-    uint32_t* bits;        // [nslots][nwords] decision words written by k_draw_bits, read by k_tab_exec
-    TabOp* d_ops; int nops;
+    uint32_t* bits;        // [nwords][slot_stride] decision words written by k_draw_bits, read by k_tab_exec
+    ExecOp* d_ops; int nops;
     TabObsArgs* d_obs; int nobs;
     double** d_stats; int nstats;
     int planes;
     plane_t* arena;        // global-memory arena, only when the shared-memory tile does not fit
     int threads, smem_bytes;
-    TabOp* h_ops;          // pinned host copy of the op list (qsb_program_upload re-sends it)
+    ExecOp* h_ops;         // pinned host copy of the op list (qsb_program_upload re-sends it)
     uint64_t ops_per_run, draws_per_run, per_traj_rows;
 };
 
-int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes) {
-    qsb_recorder* R = ctx->rec;
-    if (nplanes <= 0) nplanes = 1;
+static int rec_alloc_raw(qsb_recorder* R, int nplanes) {
     auto it = R->free_blocks.lower_bound(nplanes);
     if (it != R->free_blocks.end()) {
         int size = it->first, base = it->second;
@@ -67,10 +76,7 @@ int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes) {
     }
     return base;
 }
-void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes) {
-    if (!ctx->rec || base < 0) return;
-    if (nplanes <= 0) nplanes = 1;
-    qsb_recorder* R = ctx->rec;
+static void rec_free_raw(qsb_recorder* R, int base, int nplanes) {
     // coalesce with neighbours so that large composite states can be placed again
     for (bool merged = true; merged;) {
         merged = false;
@@ -82,10 +88,34 @@ void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes) {
     if (base + nplanes == R->next_plane) R->next_plane = base;
     else R->free_blocks.insert({nplanes, base});
 }
+int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes) {
+    qsb_recorder* R = ctx->rec;
+    if (nplanes <= 0) nplanes = 1;
+    int base = rec_alloc_raw(R, nplanes);
+    R->live[base] = (int)R->blks.size();
+    R->blks.push_back({base, R->now(), INT_MAX, {{R->now(), nplanes}}, -1, false});
+    return base;
+}
+void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes) {
+    if (!ctx->rec || base < 0) return;
+    qsb_recorder* R = ctx->rec;
+    auto it = R->live.find(base);
+    if (it == R->live.end()) return;
+    qsb_recorder::Blk& b = R->blks[it->second];
+    b.t1 = R->now();
+    rec_free_raw(R, base, b.sizes.back().second);
+    R->live.erase(it);
+}
 void qsb_rec_shrink(qsb_ctx* ctx, int base, int old_planes, int new_planes) {
-    if (old_planes <= 0) old_planes = 1;
+    qsb_recorder* R = ctx->rec;
     if (new_planes <= 0) new_planes = 1;   // a 0-qubit state keeps one (unused) plane, like a fresh allocation would
-    if (new_planes < old_planes) qsb_rec_free_planes(ctx, base + new_planes, old_planes - new_planes);
+    auto it = R->live.find(base);
+    if (it == R->live.end()) return;
+    qsb_recorder::Blk& b = R->blks[it->second];
+    int cur = b.sizes.back().second;
+    if (new_planes >= cur) return;
+    b.sizes.push_back({R->now(), new_planes});
+    rec_free_raw(R, base + new_planes, cur - new_planes);
 }
 TabOp* qsb_rec_push(qsb_ctx* ctx, int type) {
     TabOp op;
@@ -107,16 +137,6 @@ int qsb_rec_push_obs(qsb_ctx* ctx, const void* a, size_t bytes) {
 // ---------------------------------------------------------------------------------------------
 // the fused executor
 // ---------------------------------------------------------------------------------------------
-struct ExecArgs {
-    const TabOp* ops; int nops;
-    const TabObsArgs* obs;
-    const uint8_t* aux;
-    plane_t* arena;           // nullptr -> shared-memory tile
-    const plane_t* bits;      // decision bits of every stochastic op, [slot][W] (the draw pass's words seen lane-group wise)
-    const plane_t* valid;
-    size_t W;                 // lane groups (threads) in the ensemble = trajectories / QSB_LANES
-    uint64_t seed, traj0, draw_base;
-};
 
 __global__ void k_zero_stats(double* const* ptrs, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -127,217 +147,69 @@ __global__ void k_zero_stats(double* const* ptrs, int n) {
 // ballot packs the 32 decisions of a word, so the bit-sliced pass below never runs Philox (which a
 // thread-per-word kernel would have to loop over its 32 lanes for, at 1/32 of the parallelism).
 __global__ void __launch_bounds__(256) k_draw_bits(const DrawSpec* __restrict__ specs, int nspecs, uint32_t* __restrict__ bits,
-                                                   size_t W, uint64_t seed, uint64_t traj0, uint64_t draw_base) {
+                                                   size_t W, int slot_stride, uint64_t seed, uint64_t traj0, uint64_t draw_base) {
+    __shared__ DrawSpec sspec[QSB_DRAW_CHUNK];
     const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;   // local trajectory; W*32 is a multiple of 32
-    if (t >= W * 32) return;                                          // whole warps leave together
-    const size_t wg = t >> 5;
+    const bool on = t < W * 32;                                       // whole warps are on or off together
     const unsigned lane = threadIdx.x & 31u;
+    uint32_t* row = bits + (on ? (t >> 5) : 0) * (size_t)slot_stride; // this word's slots are contiguous: slot order = spec order
+    // decision words wait in registers (lane l holds the l-th pending word) until 32 of them go out as one 128-byte store
+    uint32_t mine = 0;
+    unsigned fill = 0;
     const uint64_t traj = traj0 + t;
-    for (int i = 0; i < nspecs; ++i) {
-        const DrawSpec& s = specs[i];
-        const double u = qsb_draw(seed, traj, s.draw + draw_base);
-        uint32_t d;
-        if (s.type == TOP_NOISE) {
-            d = 0;
-            for (int j = 0; j < s.np; ++j) if (u > s.cum[j]) { int P = s.op[j]; d = ((P == 1 || P == 2) ? 1u : 0u) | ((P == 3 || P == 2) ? 2u : 0u); break; }
-        } else if (s.type == TOP_SELECT) {
-            d = (uint32_t)(s.np - 1);
-            for (int j = 0; j < s.np; ++j) if (s.cum[j] > u) { d = (uint32_t)j; break; }
-        } else if (s.type == TOP_MEASURE) {
-            d = u >= 0.5 ? 1u : 0u;
-        } else {
-            d = u < s.cum[0] ? 1u : 0u;
-        }
-        const uint32_t b0 = __ballot_sync(0xffffffffu, d & 1u);
-        uint32_t* dst = bits + (size_t)s.slot * W + wg;
-        if (s.type == TOP_NOISE) {
-            const uint32_t b1 = __ballot_sync(0xffffffffu, d & 2u);
-            if (lane == 0) { dst[0] = b0; dst[W] = b1; }
-        } else if (s.type == TOP_SELECT) {
-            const uint32_t b1 = __ballot_sync(0xffffffffu, d & 2u), b2 = __ballot_sync(0xffffffffu, d & 4u);
-            if (lane == 0) { dst[0] = b0; dst[W] = b1; dst[2 * W] = b2; }
-        } else if (lane == 0) dst[0] = b0;
-    }
-}
-
-// The tableau functions are force-inlined with a LITERAL qubit count so that their loops unroll and their
-// per-row scratch arrays live in registers (a run-time n keeps them in local memory: 2.2 KB of stack per thread).
-#define N_CASE(K, ...) case K: { constexpr int N = K; __VA_ARGS__; } break;
-#define N_SWITCH(NV, ...) switch (NV) { N_CASE(1, __VA_ARGS__) N_CASE(2, __VA_ARGS__) N_CASE(3, __VA_ARGS__) N_CASE(4, __VA_ARGS__) \
-                                        N_CASE(5, __VA_ARGS__) default: { const int N = (NV); __VA_ARGS__; } break; }
-
-// T > 0: the arena is a [planes][T] tile of shared memory (block of T threads, compile-time stride);
-// T == 0: the arena is in global memory with stride a.W (programs whose tile exceeds the shared memory of an SM).
-template <int T>
-__global__ void __launch_bounds__(T ? T : 128) k_tab_exec(ExecArgs a) {
-    extern __shared__ plane_t tile[];
-    const size_t wg = blockIdx.x * (size_t)blockDim.x + threadIdx.x;  // global lane group (trajectories QSB_LANES*wg ..)
-    const bool on = wg < a.W;
-    plane_t* const base = T ? tile : a.arena;
-    const size_t W = T ? (size_t)T : a.W;
-    const size_t w = T ? (size_t)threadIdx.x : (on ? wg : 0);
-    const uint32_t validw = on ? a.valid[wg] : 0u;
-#define PL(idx) (base + (size_t)(idx) * W)
-    for (int i = 0; i < a.nops; ++i) {
-        const TabOp& op = a.ops[i];
-        switch (op.type) {
-        case TOP_INIT:
-            if (on) { N_SWITCH(op.n, tab_init_word(PL(op.s[0]), W, w, N, op.iv[0])) PL(op.al[0])[w] = validw; }
-            break;
-        case TOP_TENSOR:
-            if (on) {
-                if (op.n == 2 && op.n2 == 2) tab_tensor_word(PL(op.s[0]), PL(op.s[1]), PL(op.s[2]), W, w, 2, 2);
-                else tab_tensor_word(PL(op.s[0]), PL(op.s[1]), PL(op.s[2]), W, w, op.n, op.n2);
-                PL(op.al[0])[w] = PL(op.al[1])[w] & PL(op.al[2])[w]; }
-            break;
-        case TOP_COPY:
-            if (on) {
-                int planes = op.n * (4 * op.n + 2);
-                for (int p = 0; p < planes; ++p) PL(op.s[0] + p)[w] = PL(op.s[1] + p)[w];
-                PL(op.al[0])[w] = PL(op.al[1])[w];
+    uint32_t blk[4];
+    uint64_t have = ~0ull;   // Philox block currently in registers (two draws per block)
+    auto push = [&](uint32_t word) {
+        if (lane == fill) mine = word;
+        if (++fill == 32) { if (on) row[lane] = mine; row += 32; fill = 0; }
+    };
+    for (int i0 = 0; i0 < nspecs; i0 += QSB_DRAW_CHUNK) {
+        __syncthreads();
+        const int nc = min(QSB_DRAW_CHUNK, nspecs - i0);
+        for (int k = threadIdx.x; k < nc * (int)(sizeof(DrawSpec) / 16); k += blockDim.x)
+            reinterpret_cast<uint4*>(sspec)[k] = __ldg(reinterpret_cast<const uint4*>(specs + i0) + k);
+        __syncthreads();
+        for (int i = 0; i < nc; ++i) {
+            const DrawSpec& s = sspec[i];
+            const uint64_t id = s.draw + draw_base;
+            if ((id >> 1) != have) { have = id >> 1; qsb_philox_block(seed, traj, have, blk); }
+            const uint64_t k = ((id & 1) ? (((uint64_t)blk[3] << 32) | blk[2]) : (((uint64_t)blk[1] << 32) | blk[0])) >> 11;   // u = k / 2^53
+            if (s.type == TOP_NOISE) {
+                if (!__any_sync(0xffffffffu, k > s.thr_any)) { push(0u); push(0u); continue; }   // the common case: nobody errs
+                uint32_t d = 0;
+                for (int j = s.np - 1; j >= 0; --j) if (k > s.thr[j]) d = s.code[j];   // first matching branch wins (thr descends)
+                push(__ballot_sync(0xffffffffu, d & 1u));
+                push(__ballot_sync(0xffffffffu, d & 2u));
+            } else if (s.type == TOP_SELECT) {
+                uint32_t d = (uint32_t)(s.np - 1);
+                for (int j = s.np - 2; j >= 0; --j) if (k < s.thr[j]) d = (uint32_t)j;           // first j with u < cum[j]
+                push(__ballot_sync(0xffffffffu, d & 1u));
+                push(__ballot_sync(0xffffffffu, d & 2u));
+                push(__ballot_sync(0xffffffffu, d & 4u));
+            } else {
+                const bool below = k < s.thr[0];   // measurement: thr = 2^52, bit = !(u < 0.5); random mask: bit = u < p
+                push(__ballot_sync(0xffffffffu, s.type == TOP_MEASURE ? !below : below));
             }
-            break;
-        case TOP_SELECT:
-            if (on) {
-                uint32_t m[5];
-                const plane_t* d = a.bits + (size_t)op.dslot * a.W + wg;
-                const uint32_t b0 = d[0], b1 = d[a.W], b2 = d[2 * a.W];   // bit planes of the selected index
-                for (int j = 0; j < 5; ++j) m[j] = ((j & 1) ? b0 : ~b0) & ((j & 2) ? b1 : ~b1) & ((j & 4) ? b2 : ~b2);
-                int planes = op.n * (4 * op.n + 2);
-                for (int p = 0; p < planes; ++p) {
-                    uint32_t v = 0;
-                    for (int j = 0; j < op.n2; ++j) v |= m[j] & PL(op.s[1 + j] + p)[w];
-                    PL(op.s[0] + p)[w] = v;
-                }
-                uint32_t al = 0;
-                for (int j = 0; j < op.n2; ++j) al |= m[j] & PL(op.al[1 + j])[w];
-                PL(op.al[0])[w] = al;
-            }
-            break;
-        case TOP_SELECT_CONST:
-            if (on) {
-                uint32_t m[5];
-                const plane_t* d = a.bits + (size_t)op.dslot * a.W + wg;
-                const uint32_t b0 = d[0], b1 = d[a.W], b2 = d[2 * a.W];
-                for (int j = 0; j < 5; ++j) m[j] = ((j & 1) ? b0 : ~b0) & ((j & 2) ? b1 : ~b1) & ((j & 4) ? b2 : ~b2);
-                const uint8_t* tab = a.aux + op.obs;
-                const int planes = op.n * (4 * op.n + 2);
-                for (int p = 0; p < planes; ++p) {
-                    const uint32_t c = tab[p];
-                    uint32_t v = 0;
-                    for (int j = 0; j < 5; ++j) v |= ((c >> j) & 1) ? m[j] : 0u;
-                    PL(op.s[0] + p)[w] = (plane_t)v;
-                }
-                PL(op.al[0])[w] = (plane_t)validw;
-            }
-            break;
-        case TOP_GATE:
-            if (on) {
-                const uint32_t gm = op.m[0] >= 0 ? (uint32_t)PL(op.m[0])[w] : QSB_FULL;
-                N_SWITCH(op.n, tab_gate_anf(PL(op.s[0]), W, w, N, op.k, op.q[0], op.q[1], op.outmask, op.u[0], gm))
-            }
-            break;
-        case TOP_NOISE:
-            if (on) {
-                const plane_t* d = a.bits + (size_t)op.dslot * a.W + wg;
-                const uint32_t fx = d[0], fz = d[a.W];
-                N_SWITCH(op.n, tab_noise_apply(PL(op.s[0]), W, w, N, op.q[0], fx, fz))
-            }
-            break;
-        case TOP_MEASURE:
-            if (on) {
-                uint32_t rnd;
-                uint32_t outcome = 0; const uint32_t rb = a.bits[(size_t)op.dslot * a.W + wg];
-                N_SWITCH(op.n, outcome = tab_measure_bits(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0], op.iv[0], op.iv[1], rb, &rnd))
-                uint32_t al = PL(op.al[1])[w];
-                PL(op.m[0])[w] = outcome & al;
-                if (op.m[1] >= 0) PL(op.m[1])[w] = rnd & al;
-            }
-            break;
-        case TOP_PTRACE:
-            if (on) { N_SWITCH(op.n, tab_ptrace_word(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0])) }
-            break;
-        case TOP_FORCE:
-            if (on) { N_SWITCH(op.n, tab_force_word(PL(op.s[0]), W, w, N, op.u[0], op.u[1], op.iv[0])) }
-            break;
-        case TOP_EXPECT: {
-            // integer tallies (exact, order independent): alive lanes, sum of (plus - minus), sum of its square
-            int n_alive = 0, num = 0, num2 = 0;
-            int nelem = 1;
-            if (on) {
-                const TabObsArgs& o = a.obs[op.obs];
-                nelem = o.nelem;
-                uint32_t cnt[8], cntm[8];
-                N_SWITCH(op.n, tab_expect_word_n(PL(op.s[0]), W, w, N, o, cnt, cntm))
-                const uint32_t al = PL(op.al[0])[w];
-                n_alive = __popc(al);
-                if (nelem == 1 && !op.per_traj) {   // a single Pauli: each lane holds -1, 0 or +1
-                    num = __popc(cnt[0] & al) - __popc(cntm[0] & al);
-                    num2 = __popc((cnt[0] | cntm[0]) & al);
-                } else {
-                    const double inv = 1.0 / (double)nelem;
-                    for (int l = 0; l < QSB_LANES; ++l) {
-                        int plus = 0, minus = 0;
-                        for (int b = 0; b < 8; ++b) { plus |= ((cnt[b] >> l) & 1) << b; minus |= ((cntm[b] >> l) & 1) << b; }
-                        const bool lane = (al >> l) & 1u;
-                        const int d = lane ? plus - minus : 0;
-                        if (op.per_traj) { size_t t = wg * QSB_LANES + l; op.per_traj[2 * t] = (double)d * inv; op.per_traj[2 * t + 1] = 0.0; }
-                        num += d; num2 += d * d;
-                    }
-                }
-            }
-            if (op.stats) {  // whole warps reach this point together (the op list is uniform)
-                n_alive = __reduce_add_sync(0xffffffffu, n_alive);
-                num = __reduce_add_sync(0xffffffffu, num);
-                num2 = __reduce_add_sync(0xffffffffu, num2);
-                nelem = __reduce_max_sync(0xffffffffu, nelem);
-                if ((threadIdx.x & 31) == 0 && n_alive) {
-                    const double inv = 1.0 / (double)nelem;   // nelem = 2^k: the scaled tallies are exact
-                    atomicAdd(&op.stats[0], (double)n_alive); atomicAdd(&op.stats[1], (double)num * inv); atomicAdd(&op.stats[2], (double)num2 * inv * inv);
-                }
-            }
-            break;
-        }
-        case TOP_MASK_FILL:
-            if (on) PL(op.m[0])[w] = op.iv[0] ? validw : 0u;
-            break;
-        case TOP_MASK_LOGIC:
-            if (on) {
-                uint32_t x = PL(op.m[1])[w], y = op.m[2] >= 0 ? PL(op.m[2])[w] : 0u, r;
-                switch (op.iv[0]) {
-                    case QSB_MASK_AND: r = x & y; break;
-                    case QSB_MASK_OR: r = x | y; break;
-                    case QSB_MASK_XOR: r = x ^ y; break;
-                    case QSB_MASK_ANDNOT: r = x & ~y; break;
-                    case QSB_MASK_NOT: r = ~x; break;
-                    default: r = ~(x ^ y); break;
-                }
-                PL(op.m[0])[w] = (plane_t)(r & validw);
-            }
-            break;
-        case TOP_MASK_RANDOM:
-            if (on) {
-                PL(op.m[0])[w] = a.bits[(size_t)op.dslot * a.W + wg] & validw;
-            }
-            break;
-        case TOP_KILL:
-            if (on) PL(op.al[0])[w] = (plane_t)(PL(op.al[0])[w] & ~PL(op.m[0])[w]);
-            break;
-        case TOP_ALIVE_COPY:
-            if (on) PL(op.m[0])[w] = PL(op.al[0])[w];
-            break;
         }
     }
-#undef PL
+    if (on && lane < fill) row[lane] = mine;
 }
 
-typedef void (*exec_fn)(ExecArgs);
-static exec_fn exec_kernel(int threads, bool global_arena) {
-    if (global_arena) return k_tab_exec<0>;
+// the per-block-size instantiations live in qsb_exec_inst.cu (one object per size, csrc/Makefile)
+#define QSB_EXEC_SIZES(X) X(32) X(64) X(96) X(128) X(256)
+#define X(T) cudaError_t qsb_exec_launch_##T(const ExecArgs&, unsigned, int, cudaStream_t);
+QSB_EXEC_SIZES(X) X(0)
+#undef X
+const int qsb_exec_block_sizes[] = {
+#define X(T) T,
+    QSB_EXEC_SIZES(X)
+#undef X
+    0};
+qsb_exec_launch_fn qsb_exec_launcher(int threads) {
     switch (threads) {
-        case 64: return k_tab_exec<64>;
-        case 128: return k_tab_exec<128>;
-        case 256: return k_tab_exec<256>;
+#define X(T) case T: return qsb_exec_launch_##T;
+        QSB_EXEC_SIZES(X) X(0)
+#undef X
         default: return nullptr;
     }
 }
@@ -409,6 +281,86 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
                 it = used ? pend.erase(it) : std::next(it);
             }
         }
+        // Offline re-packing of the arena.  The online allocator had to number planes while the schedule was still
+        // unfolding; now every block's lifetime is known, blocks only the folded ops touched can be dropped, and
+        // the rest is placed big-blocks-first at the lowest offset free during its whole lifetime.  A smaller arena
+        // means more resident threads per SM (the tile is [planes][threads] of shared memory).
+        {
+            typedef qsb_recorder::Blk Blk;
+            std::vector<Blk>& B = R->blks;
+            const int nops = (int)R->ops.size();
+            auto size_at = [](const Blk& b, int t) { int sz = b.sizes[0].second; for (auto& e : b.sizes) if (e.first <= t) sz = e.second; return sz; };
+            auto find_blk = [&](int plane, int t) -> int {
+                for (int k = 0; k < (int)B.size(); ++k) if (B[k].t0 <= t && t < B[k].t1 && plane >= B[k].base && plane < B[k].base + size_at(B[k], t)) return k;
+                return -1;
+            };
+            for (int i = 0; i < nops; ++i) {
+                const TabOp& o = R->ops[i];
+                if (o.type == TOP_NOP) continue;
+                for (int k = 0; k < 6; ++k) { if (o.s[k] >= 0) { int b = find_blk(o.s[k], i); if (b >= 0) B[b].used = true; } if (o.al[k] >= 0) { int b = find_blk(o.al[k], i); if (b >= 0) B[b].used = true; } }
+                for (int k = 0; k < 3; ++k) if (o.m[k] >= 0) { int b = find_blk(o.m[k], i); if (b >= 0) B[b].used = true; }
+            }
+            auto conflict = [&](const Blk& x, int xo, const Blk& y, int yo) {
+                int lo = std::max(x.t0, y.t0), hi = std::min(x.t1, y.t1);
+                if (lo >= hi) return -1;
+                // sizes only shrink: the pair overlaps at some common time iff it does at the first common time
+                // or at any later step of either staircase; check every breakpoint inside [lo, hi)
+                std::vector<int> ts{lo};
+                for (auto& e : x.sizes) if (e.first > lo && e.first < hi) ts.push_back(e.first);
+                for (auto& e : y.sizes) if (e.first > lo && e.first < hi) ts.push_back(e.first);
+                int need = -1;   // lowest offset for x that clears y at every conflicting time, -1: no conflict
+                for (int t : ts) { int xs = size_at(x, t), ys = size_at(y, t); if (xo < yo + ys && yo < xo + xs) need = std::max(need, yo + ys); }
+                return need;
+            };
+            std::vector<int> order;
+            for (int k = 0; k < (int)B.size(); ++k) if (B[k].used) order.push_back(k);
+            // several placement orders, keep the tightest: long-lived blocks first (temporaries stack on top),
+            // big blocks first, and allocation order
+            auto life = [&](int k) { return (long)std::min(B[k].t1, nops) - B[k].t0; };
+            auto place = [&](const std::vector<int>& ord, std::vector<int>& nb) {
+                std::vector<int> placed;
+                int pk = 0;
+                for (int k : ord) {
+                    int off = 0;
+                    for (bool moved = true; moved;) {
+                        moved = false;
+                        for (int j : placed) { int need = conflict(B[k], off, B[j], nb[j]); if (need >= 0) { off = need; moved = true; } }
+                    }
+                    nb[k] = off; placed.push_back(k);
+                    pk = std::max(pk, off + B[k].sizes[0].second);
+                }
+                return pk;
+            };
+            int peak = INT_MAX;
+            for (int variant = 0; variant < 4; ++variant) {
+                std::vector<int> ord = order, nb(B.size(), -1);
+                if (variant == 0) std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return life(a) > life(b); });
+                if (variant == 1) std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return B[a].sizes[0].second > B[b].sizes[0].second; });
+                if (variant == 2) std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return life(a) * B[a].sizes[0].second > life(b) * B[b].sizes[0].second; });
+                int pk = place(ord, nb);
+                if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] packing order %d: %d planes\n", variant, pk);
+                if (pk < peak) { peak = pk; for (int k : order) B[k].nbase = nb[k]; }
+            }
+            if (order.empty()) peak = 0;
+            if (peak > 0 && peak <= P->planes && !getenv("QSB_NO_REPACK")) {
+                auto remap = [&](int& plane, int t) { if (plane < 0) return; int b = find_blk(plane, t); if (b >= 0 && B[b].used) plane = plane - B[b].base + B[b].nbase; };
+                for (int i = 0; i < nops; ++i) {
+                    TabOp& o = R->ops[i];
+                    if (o.type == TOP_NOP) continue;
+                    for (int k = 0; k < 6; ++k) { remap(o.s[k], i); remap(o.al[k], i); }
+                    for (int k = 0; k < 3; ++k) remap(o.m[k], i);
+                }
+                if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] arena re-packed: %d -> %d planes (%zu blocks)\n", P->planes, peak, order.size());
+                P->planes = peak;
+            } else if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] arena NOT re-packed: online %d planes, offline %d\n", P->planes, peak);
+            if (getenv("QSB_REC_TRACE")) {
+                int best = 0, bt = 0;
+                for (int t = 0; t < nops; ++t) { int sum = 0; for (int k : order) if (B[k].t0 <= t && t < B[k].t1) sum += size_at(B[k], t); if (sum > best) { best = sum; bt = t; } }
+                fprintf(stderr, "[rec] live-plane lower bound %d at op %d (type %d):", best, bt, R->ops[bt].type);
+                for (int k : order) if (B[k].t0 <= bt && bt < B[k].t1) fprintf(stderr, " %d[%d,%d)", size_at(B[k], bt), B[k].t0, B[k].t1 == INT_MAX ? -1 : B[k].t1);
+                fprintf(stderr, "\n");
+            }
+        }
         // drop the NOPs
         std::vector<TabOp> kept;
         for (auto& o : R->ops) if (o.type != TOP_NOP) kept.push_back(o);
@@ -423,15 +375,42 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
         DrawSpec d; memset(&d, 0, sizeof(d));
         d.draw = o.draw; d.type = o.type == TOP_SELECT_CONST ? (int)TOP_SELECT : o.type; d.slot = P->nslots;
         d.np = o.type == TOP_NOISE ? o.k : d.type == TOP_SELECT ? o.n2 : 1;
-        for (int j = 0; j < 5; ++j) d.cum[j] = o.f[j];
-        for (int j = 0; j < 3; ++j) d.op[j] = o.iv[j];
+        for (int j = 0; j < 5; ++j) {
+            const double c = o.f[j], scaled = ldexp(c < 0 ? 0.0 : (c > 1 ? 1.0 : c), 53);
+            d.thr[j] = o.type == TOP_NOISE ? (uint64_t)floor(scaled) : (uint64_t)ceil(scaled);
+        }
+        if (o.type == TOP_MEASURE) d.thr[0] = 1ull << 52;   // u >= 0.5  <=>  !(k < 2^52)
+        if (o.type == TOP_NOISE) {
+            d.thr_any = ~0ull;
+            for (int j = 0; j < d.np; ++j) {
+                if (d.thr[j] < d.thr_any) d.thr_any = d.thr[j];
+                d.code[j] = (uint8_t)(((o.iv[j] == 1 || o.iv[j] == 2) ? 1 : 0) | ((o.iv[j] == 3 || o.iv[j] == 2) ? 2 : 0));
+            }
+        }
         o.dslot = P->nslots; P->nslots += need;
         specs.push_back(d);
     }
     P->nspecs = (int)specs.size();
-    if (!R->ops.empty()) {
-        if (cudaMallocHost((void**)&P->h_ops, R->ops.size() * sizeof(TabOp)) != cudaSuccess) { cudaGetLastError(); qsb_set_error("pinned allocation of the op list failed"); rc = QSB_ERR_OOM; }
-        else memcpy(P->h_ops, R->ops.data(), R->ops.size() * sizeof(TabOp));
+    // the kernel's compact op records
+    std::vector<ExecOp> xops(R->ops.size());
+    for (size_t i = 0; i < R->ops.size() && rc == QSB_OK; ++i) {
+        const TabOp& o = R->ops[i];
+        ExecOp& x = xops[i];
+        memset(&x, 0, sizeof(x));
+        if (o.n > 255 || o.n2 > 255 || P->planes > 32767) { qsb_set_error("program too large for the executor's op encoding"); rc = QSB_ERR_UNSUPPORTED; break; }
+        x.type = (uint8_t)o.type; x.n = (uint8_t)o.n; x.n2 = (uint8_t)o.n2; x.k = (uint8_t)o.k;
+        x.q[0] = (uint8_t)o.q[0]; x.q[1] = (uint8_t)o.q[1]; x.iv[0] = (uint8_t)o.iv[0]; x.iv[1] = (uint8_t)o.iv[1];
+        for (int j = 0; j < 4; ++j) x.outmask[j] = o.outmask[j];
+        x.u[0] = o.u[0]; x.u[1] = o.u[1];
+        for (int j = 0; j < 6; ++j) { x.s[j] = (int16_t)o.s[j]; x.al[j] = (int16_t)o.al[j]; }
+        for (int j = 0; j < 3; ++j) x.m[j] = (int16_t)o.m[j];
+        x.obs = o.obs; x.dslot = o.dslot; x.stats = o.stats; x.per_traj = o.per_traj;
+    }
+    P->slot_stride = (P->nslots + 7) / 8 * 8;   // rows start on a 32-byte sector
+    if (P->slot_stride == 0) P->slot_stride = 8;
+    if (!xops.empty() && rc == QSB_OK) {
+        if (cudaMallocHost((void**)&P->h_ops, xops.size() * sizeof(ExecOp)) != cudaSuccess) { cudaGetLastError(); qsb_set_error("pinned allocation of the op list failed"); rc = QSB_ERR_OOM; }
+        else memcpy(P->h_ops, xops.data(), xops.size() * sizeof(ExecOp));
     }
     auto up = [&](void** dst, const void* src, size_t bytes) {
         if (rc != QSB_OK) return;
@@ -441,40 +420,34 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
             if (e != cudaSuccess) { qsb_set_error("program upload failed: %s", cudaGetErrorString(e)); rc = QSB_ERR_CUDA; }
         }
     };
-    up((void**)&P->d_ops, R->ops.data(), R->ops.size() * sizeof(TabOp));
+    up((void**)&P->d_ops, xops.data(), xops.size() * sizeof(ExecOp));
     up((void**)&P->d_obs, R->obs.data(), R->obs.size() * sizeof(TabObsArgs));
     up((void**)&P->d_stats, R->stats_ptrs.data(), R->stats_ptrs.size() * sizeof(double*));
     up((void**)&P->d_specs, specs.data(), specs.size() * sizeof(DrawSpec));
     up((void**)&P->d_aux, aux.data(), aux.size());
-    if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->bits, (size_t)(P->nslots ? P->nslots : 1) * ctx->nwords * sizeof(uint32_t));
+    if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->bits, (size_t)P->slot_stride * ctx->nwords * sizeof(uint32_t));
     if (rc == QSB_OK) { cudaError_t e = cudaStreamSynchronize(ctx->stream); if (e != cudaSuccess) rc = QSB_ERR_CUDA; }  // host vectors die below
     // launch shape: the largest block whose [planes][threads] tile fits, preferring a single wave
     int dev_smem = 0;
     cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
     const long groups = (long)ctx->nwords * (32 / QSB_LANES);   // one thread per lane group
-    int best_t = 0; double best_cost = 1e300;
-    for (int t = 64; t <= 256; t *= 2) {
+    // Block size: measured on B200 (tools/sweep_threads.sh) the executor is issue bound, not wave bound -- larger blocks
+    // amortise the per-chunk op staging and win slightly; take the largest block that leaves >= 2 blocks per SM.
+    int best_t = 0, best_rank = -1;
+    const char* force_t = getenv("QSB_EXEC_THREADS");   // tuning aid: pin the block size
+    for (int bi = 0; qsb_exec_block_sizes[bi]; ++bi) {
+        const int t = qsb_exec_block_sizes[bi];
+        if (force_t && atoi(force_t) != t) continue;
         size_t smem = (size_t)P->planes * t * sizeof(plane_t);
-        if (smem > (size_t)dev_smem) break;
-        int per_sm = (int)((size_t)(228 * 1024) / (smem + 1024));
-        if (per_sm < 1) per_sm = 1;
-        if (per_sm > 32) per_sm = 32;
-        if (per_sm * t > 2048) per_sm = 2048 / t;
-        long blocks = (groups + t - 1) / t;
-        long slots = (long)ctx->sm_count * per_sm;
-        long waves = (blocks + slots - 1) / slots;
-        // a wave costs about one thread's serial time; more resident warps per SM stretch it only a little
-        double cost = (double)waves * (1.0 + 0.01 * per_sm * t / 32.0);
-        if (cost < best_cost) { best_cost = cost; best_t = t; }
+        if (smem > (size_t)dev_smem) continue;
+        int per_sm = (int)((size_t)(228 * 1024) / (smem + 1024 + QSB_EXEC_CHUNK * sizeof(ExecOp)));
+        int rank = (per_sm >= 2 ? 1000 : 0) + t;
+        if (rank > best_rank) { best_rank = rank; best_t = t; }
     }
     if (best_t) { P->threads = best_t; P->smem_bytes = P->planes * best_t * (int)sizeof(plane_t); P->arena = nullptr; }
     else {
         P->threads = 128; P->smem_bytes = 0;
         if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->arena, (size_t)P->planes * groups * sizeof(plane_t));
-    }
-    if (rc == QSB_OK && P->smem_bytes) {
-        cudaError_t e = cudaFuncSetAttribute(exec_kernel(P->threads, P->arena != nullptr), cudaFuncAttributeMaxDynamicSharedMemorySize, P->smem_bytes);
-        if (e != cudaSuccess) { qsb_set_error("cudaFuncSetAttribute(%d bytes) failed: %s", P->smem_bytes, cudaGetErrorString(e)); rc = QSB_ERR_CUDA; }
     }
     delete R;
     ctx->rec = nullptr;
@@ -496,21 +469,26 @@ extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t dra
     ExecArgs a;
     a.ops = P->d_ops; a.nops = P->nops; a.obs = P->d_obs; a.aux = P->d_aux; a.arena = P->arena; a.valid = (const plane_t*)ctx->valid; a.W = (size_t)ctx->nwords * (32 / QSB_LANES);
     a.seed = ctx->seed; a.traj0 = (uint64_t)ctx->traj_offset + traj_shift; a.draw_base = draw_base;
-    a.bits = (const plane_t*)P->bits;
+    a.bits = P->bits; a.slot_stride = P->slot_stride;
     if (P->nspecs) {
         QSB_PRE(ctx, "k_draw_bits");
-        k_draw_bits<<<(unsigned)((ctx->nwords * 32 + 255) / 256), 256, 0, ctx->stream>>>(P->d_specs, P->nspecs, P->bits, (size_t)ctx->nwords, a.seed, a.traj0, draw_base);
+        k_draw_bits<<<(unsigned)((ctx->nwords * 32 + 255) / 256), 256, 0, ctx->stream>>>(P->d_specs, P->nspecs, P->bits, (size_t)ctx->nwords, P->slot_stride, a.seed, a.traj0, draw_base);
         QSB_LAUNCH_CHECK(ctx);
         // decision words: written once by the draw pass, read once by the executor
         qsb_account(ctx, "k_draw_bits", (uint64_t)P->nslots * ctx->nwords * 4 + (uint64_t)P->nspecs * sizeof(DrawSpec));
     }
     unsigned blocks = (unsigned)((a.W + P->threads - 1) / P->threads);
     QSB_PRE(ctx, "k_tab_exec");
-    exec_kernel(P->threads, P->arena != nullptr)<<<blocks, P->threads, P->smem_bytes, ctx->stream>>>(a);
+    {
+        qsb_exec_launch_fn launch = qsb_exec_launcher(P->arena ? 0 : P->threads);
+        if (!launch) QSB_FAIL(QSB_ERR_BAD_ARG, "no executor compiled for %d threads per block", P->threads);
+        cudaError_t e = launch(a, blocks, P->smem_bytes, ctx->stream);
+        if (e != cudaSuccess) QSB_FAIL(QSB_ERR_CUDA, "k_tab_exec launch failed: %s", cudaGetErrorString(e));
+    }
     QSB_LAUNCH_CHECK(ctx);
     // compulsory HBM traffic of the fused launch: the op list and the valid words once, the statistics rows and
     // any per-trajectory observable rows written once -- the ensemble state itself never leaves the SM
-    qsb_account(ctx, "k_tab_exec", (uint64_t)P->nops * sizeof(TabOp) + (uint64_t)ctx->nwords * 4 + (uint64_t)P->nstats * 32 + (uint64_t)P->nslots * ctx->nwords * 4 +
+    qsb_account(ctx, "k_tab_exec", (uint64_t)P->nops * sizeof(ExecOp) + (uint64_t)ctx->nwords * 4 + (uint64_t)P->nstats * 32 + (uint64_t)P->nslots * ctx->nwords * 4 +
                                        P->per_traj_rows * (uint64_t)ctx->npad * 16);
     ctx->ops += P->ops_per_run; ctx->draws += P->draws_per_run;
     return QSB_OK;
@@ -520,7 +498,7 @@ extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t dra
 // program's only host-side input, so an end-to-end timing that starts from host buffers includes this copy.
 extern "C" int qsb_program_upload(qsb_program* P, int64_t* bytes) {
     if (!P) QSB_FAIL(QSB_ERR_BAD_ARG, "null program");
-    size_t b = (size_t)P->nops * sizeof(TabOp);
+    size_t b = (size_t)P->nops * sizeof(ExecOp);
     if (b) QSB_CUDA(cudaMemcpyAsync(P->d_ops, P->h_ops, b, cudaMemcpyHostToDevice, P->ctx->stream));
     if (bytes) *bytes = (int64_t)b;
     return QSB_OK;

@@ -1,0 +1,200 @@
+// qsb_exec_inst.cu -- one instantiation of the fused executor kernel per compilation (-DQSB_EXEC_T=<threads>).
+#include "qsb_exec_kernel.cuh"
+#ifndef QSB_EXEC_T
+#error "compile with -DQSB_EXEC_T=<threads per block> (0 = arena in global memory)"
+#endif
+
+// The tableau functions are force-inlined with a LITERAL qubit count so that their loops unroll and their
+// per-row scratch arrays live in registers (a run-time n keeps them in local memory: 2.2 KB of stack per thread).
+#define N_CASE(K, ...) case K: { constexpr int N = K; __VA_ARGS__; } break;
+#define N_SWITCH(NV, ...) switch (NV) { N_CASE(1, __VA_ARGS__) N_CASE(2, __VA_ARGS__) N_CASE(3, __VA_ARGS__) N_CASE(4, __VA_ARGS__) \
+                                        N_CASE(5, __VA_ARGS__) default: { const int N = (NV); __VA_ARGS__; } break; }
+
+// T > 0: the arena is a [planes][T] tile of shared memory (block of T threads, compile-time stride);
+// T == 0: the arena is in global memory with stride a.W (programs whose tile exceeds the shared memory of an SM).
+template <int T>
+__global__ void __launch_bounds__(T ? T : 128) k_tab_exec(ExecArgs a) {
+    extern __shared__ plane_t tile[];
+    const size_t wg = blockIdx.x * (size_t)blockDim.x + threadIdx.x;  // global lane group (trajectories QSB_LANES*wg ..)
+    const bool on = wg < a.W;
+    plane_t* const base = T ? tile : a.arena;
+    const size_t W = T ? (size_t)T : a.W;
+    const size_t w = T ? (size_t)threadIdx.x : (on ? wg : 0);
+    const uint32_t validw = on ? a.valid[wg] : 0u;
+#define PL(idx) (base + (size_t)(idx) * W)
+    // decision bits of this thread's lanes: word-major rows, the lanes sit at bit `bshift` of each 32-bit word
+    const uint32_t* const brow = a.bits + (on ? wg / (32 / QSB_LANES) : 0) * (size_t)a.slot_stride;
+    const int bshift = (int)(wg % (32 / QSB_LANES)) * QSB_LANES;
+#define DBITS(slot) ((__ldg(brow + (slot)) >> bshift) & QSB_FULL)
+    __shared__ ExecOp sops[QSB_EXEC_CHUNK];
+    for (int i = 0; i < a.nops; ++i) {
+        if ((i % QSB_EXEC_CHUNK) == 0) {   // refill: the whole block copies the next chunk of ops (coalesced 16-byte loads)
+            __syncthreads();
+            const int nchunk = min(QSB_EXEC_CHUNK, a.nops - i);
+            const uint4* src = reinterpret_cast<const uint4*>(a.ops + i);
+            uint4* dst = reinterpret_cast<uint4*>(sops);
+            for (int k = threadIdx.x; k < nchunk * (int)(sizeof(ExecOp) / 16); k += blockDim.x) dst[k] = __ldg(src + k);
+            __syncthreads();
+        }
+        const ExecOp& op = sops[i % QSB_EXEC_CHUNK];
+        switch (op.type) {
+        case TOP_INIT:
+            if (on) { N_SWITCH(op.n, tab_init_word(PL(op.s[0]), W, w, N, op.iv[0])) PL(op.al[0])[w] = validw; }
+            break;
+        case TOP_TENSOR:
+            if (on) {
+                if (op.n == 2 && op.n2 == 2) tab_tensor_word(PL(op.s[0]), PL(op.s[1]), PL(op.s[2]), W, w, 2, 2);
+                else tab_tensor_word(PL(op.s[0]), PL(op.s[1]), PL(op.s[2]), W, w, op.n, op.n2);
+                PL(op.al[0])[w] = PL(op.al[1])[w] & PL(op.al[2])[w]; }
+            break;
+        case TOP_COPY:
+            if (on) {
+                int planes = op.n * (4 * op.n + 2);
+                for (int p = 0; p < planes; ++p) PL(op.s[0] + p)[w] = PL(op.s[1] + p)[w];
+                PL(op.al[0])[w] = PL(op.al[1])[w];
+            }
+            break;
+        case TOP_SELECT:
+            if (on) {
+                uint32_t m[5];
+                const uint32_t b0 = DBITS(op.dslot), b1 = DBITS(op.dslot + 1), b2 = DBITS(op.dslot + 2);   // bit planes of the selected index
+                for (int j = 0; j < 5; ++j) m[j] = ((j & 1) ? b0 : ~b0) & ((j & 2) ? b1 : ~b1) & ((j & 4) ? b2 : ~b2);
+                int planes = op.n * (4 * op.n + 2);
+                for (int p = 0; p < planes; ++p) {
+                    uint32_t v = 0;
+                    for (int j = 0; j < op.n2; ++j) v |= m[j] & PL(op.s[1 + j] + p)[w];
+                    PL(op.s[0] + p)[w] = v;
+                }
+                uint32_t al = 0;
+                for (int j = 0; j < op.n2; ++j) al |= m[j] & PL(op.al[1 + j])[w];
+                PL(op.al[0])[w] = al;
+            }
+            break;
+        case TOP_SELECT_CONST:
+            if (on) {
+                uint32_t m[5];
+                const uint32_t b0 = DBITS(op.dslot), b1 = DBITS(op.dslot + 1), b2 = DBITS(op.dslot + 2);
+                for (int j = 0; j < 5; ++j) m[j] = ((j & 1) ? b0 : ~b0) & ((j & 2) ? b1 : ~b1) & ((j & 4) ? b2 : ~b2);
+                const uint8_t* tab = a.aux + op.obs;
+                const int planes = op.n * (4 * op.n + 2);
+                for (int p = 0; p < planes; ++p) {
+                    const uint32_t c = tab[p];
+                    uint32_t v = 0;
+                    for (int j = 0; j < 5; ++j) v |= ((c >> j) & 1) ? m[j] : 0u;
+                    PL(op.s[0] + p)[w] = (plane_t)v;
+                }
+                PL(op.al[0])[w] = (plane_t)validw;
+            }
+            break;
+        case TOP_GATE:
+            if (on) {
+                const uint32_t gm = op.m[0] >= 0 ? (uint32_t)PL(op.m[0])[w] : QSB_FULL;
+                N_SWITCH(op.n, tab_gate_anf(PL(op.s[0]), W, w, N, op.k, op.q[0], op.q[1], op.outmask, op.u[0], gm))
+            }
+            break;
+        case TOP_NOISE:
+            if (on) {
+                const uint32_t fx = DBITS(op.dslot), fz = DBITS(op.dslot + 1);
+                N_SWITCH(op.n, tab_noise_apply(PL(op.s[0]), W, w, N, op.q[0], fx, fz))
+            }
+            break;
+        case TOP_MEASURE:
+            if (on) {
+                uint32_t rnd;
+                uint32_t outcome = 0; const uint32_t rb = DBITS(op.dslot);
+                N_SWITCH(op.n, outcome = tab_measure_bits(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0], op.iv[0], op.iv[1], rb, &rnd))
+                uint32_t al = PL(op.al[1])[w];
+                PL(op.m[0])[w] = outcome & al;
+                if (op.m[1] >= 0) PL(op.m[1])[w] = rnd & al;
+            }
+            break;
+        case TOP_PTRACE:
+            if (on) { N_SWITCH(op.n, tab_ptrace_word(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0])) }
+            break;
+        case TOP_FORCE:
+            if (on) { N_SWITCH(op.n, tab_force_word(PL(op.s[0]), W, w, N, op.u[0], op.u[1], op.iv[0])) }
+            break;
+        case TOP_EXPECT: {
+            // integer tallies (exact, order independent): alive lanes, sum of (plus - minus), sum of its square
+            int n_alive = 0, num = 0, num2 = 0;
+            int nelem = 1;
+            if (on) {
+                const TabObsArgs& o = a.obs[op.obs];
+                nelem = o.nelem;
+                uint32_t cnt[8], cntm[8];
+                N_SWITCH(op.n, tab_expect_word_n(PL(op.s[0]), W, w, N, o, cnt, cntm))
+                const uint32_t al = PL(op.al[0])[w];
+                n_alive = __popc(al);
+                if (nelem == 1 && !op.per_traj) {   // a single Pauli: each lane holds -1, 0 or +1
+                    num = __popc(cnt[0] & al) - __popc(cntm[0] & al);
+                    num2 = __popc((cnt[0] | cntm[0]) & al);
+                } else {
+                    const double inv = 1.0 / (double)nelem;
+                    for (int l = 0; l < QSB_LANES; ++l) {
+                        int plus = 0, minus = 0;
+                        for (int b = 0; b < 8; ++b) { plus |= ((cnt[b] >> l) & 1) << b; minus |= ((cntm[b] >> l) & 1) << b; }
+                        const bool lane = (al >> l) & 1u;
+                        const int d = lane ? plus - minus : 0;
+                        if (op.per_traj) { size_t t = wg * QSB_LANES + l; op.per_traj[2 * t] = (double)d * inv; op.per_traj[2 * t + 1] = 0.0; }
+                        num += d; num2 += d * d;
+                    }
+                }
+            }
+            if (op.stats) {  // whole warps reach this point together (the op list is uniform)
+                n_alive = __reduce_add_sync(0xffffffffu, n_alive);
+                num = __reduce_add_sync(0xffffffffu, num);
+                num2 = __reduce_add_sync(0xffffffffu, num2);
+                nelem = __reduce_max_sync(0xffffffffu, nelem);
+                if ((threadIdx.x & 31) == 0 && n_alive) {
+                    const double inv = 1.0 / (double)nelem;   // nelem = 2^k: the scaled tallies are exact
+                    atomicAdd(&op.stats[0], (double)n_alive); atomicAdd(&op.stats[1], (double)num * inv); atomicAdd(&op.stats[2], (double)num2 * inv * inv);
+                }
+            }
+            break;
+        }
+        case TOP_MASK_FILL:
+            if (on) PL(op.m[0])[w] = op.iv[0] ? validw : 0u;
+            break;
+        case TOP_MASK_LOGIC:
+            if (on) {
+                uint32_t x = PL(op.m[1])[w], y = op.m[2] >= 0 ? PL(op.m[2])[w] : 0u, r;
+                switch (op.iv[0]) {
+                    case QSB_MASK_AND: r = x & y; break;
+                    case QSB_MASK_OR: r = x | y; break;
+                    case QSB_MASK_XOR: r = x ^ y; break;
+                    case QSB_MASK_ANDNOT: r = x & ~y; break;
+                    case QSB_MASK_NOT: r = ~x; break;
+                    default: r = ~(x ^ y); break;
+                }
+                PL(op.m[0])[w] = (plane_t)(r & validw);
+            }
+            break;
+        case TOP_MASK_RANDOM:
+            if (on) {
+                PL(op.m[0])[w] = (plane_t)(DBITS(op.dslot) & validw);
+            }
+            break;
+        case TOP_KILL:
+            if (on) PL(op.al[0])[w] = (plane_t)(PL(op.al[0])[w] & ~PL(op.m[0])[w]);
+            break;
+        case TOP_ALIVE_COPY:
+            if (on) PL(op.m[0])[w] = PL(op.al[0])[w];
+            break;
+        }
+    }
+#undef PL
+#undef DBITS
+}
+
+#define QSB_CAT2(a, b) a##b
+#define QSB_CAT(a, b) QSB_CAT2(a, b)
+cudaError_t QSB_CAT(qsb_exec_launch_, QSB_EXEC_T)(const ExecArgs& a, unsigned blocks, int smem_bytes, cudaStream_t stream) {
+    static int configured = -1;
+    if (smem_bytes > configured) {
+        cudaError_t e = cudaFuncSetAttribute(k_tab_exec<QSB_EXEC_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+        if (e != cudaSuccess) return e;
+        configured = smem_bytes;
+    }
+    k_tab_exec<QSB_EXEC_T><<<blocks, QSB_EXEC_T ? QSB_EXEC_T : 128, smem_bytes, stream>>>(a);
+    return cudaGetLastError();
+}

@@ -34,8 +34,11 @@ QSB_HD uint32_t qsb_mulhi32(uint32_t a, uint32_t b) {
 #endif
 }
 // Philox4x32-10; identical to the oracle's qso_draw (the "injected draw").
-QSB_HD double qsb_draw(uint64_t seed, uint64_t traj, uint64_t draw_id) {
-    uint32_t c0 = (uint32_t)traj, c1 = (uint32_t)(traj >> 32), c2 = (uint32_t)draw_id, c3 = (uint32_t)(draw_id >> 32);
+// One Philox block = 128 bits = TWO 53-bit uniforms: draw 2b uses words (0,1), draw 2b+1 words (2,3) of the block with
+// counter (trajectory, b).  Consecutive draw ids of a trajectory therefore share one block (the fused draw pass
+// keeps it in registers); a lone draw costs the same ten rounds as before.
+QSB_HD void qsb_philox_block(uint64_t seed, uint64_t traj, uint64_t block, uint32_t* out) {
+    uint32_t c0 = (uint32_t)traj, c1 = (uint32_t)(traj >> 32), c2 = (uint32_t)block, c3 = (uint32_t)(block >> 32);
     uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
     for (int r = 0; r < 10; ++r) {
         uint32_t h0 = qsb_mulhi32(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
@@ -44,14 +47,23 @@ QSB_HD double qsb_draw(uint64_t seed, uint64_t traj, uint64_t draw_id) {
         c0 = n0; c1 = l1; c2 = n2; c3 = l0;
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
     }
-    uint64_t bits = ((uint64_t)c1 << 32) | c0;
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+QSB_HD double qsb_uniform53(uint32_t lo, uint32_t hi) {
+    uint64_t bits = ((uint64_t)hi << 32) | lo;
     return (double)(bits >> 11) * (1.0 / 9007199254740992.0);
+}
+QSB_HD double qsb_draw(uint64_t seed, uint64_t traj, uint64_t draw_id) {
+    uint32_t o[4];
+    qsb_philox_block(seed, traj, draw_id >> 1, o);
+    return (draw_id & 1) ? qsb_uniform53(o[2], o[3]) : qsb_uniform53(o[0], o[1]);
 }
 
 struct TabView {
-    plane_t* p; size_t W; size_t w; int n; int S;
-    QSB_HD uint32_t ld(int plane) const { return (uint32_t)p[(size_t)plane * W + w]; }
-    QSB_HD void st(int plane, uint32_t v) const { p[(size_t)plane * W + w] = (plane_t)v; }
+    plane_t* p;   // this thread's column: plane k of the state is p[k * W]
+    size_t W; int n; int S;
+    QSB_HD uint32_t ld(int plane) const { return (uint32_t)p[(size_t)(unsigned)plane * W]; }
+    QSB_HD void st(int plane, uint32_t v) const { p[(size_t)(unsigned)plane * W] = (plane_t)v; }
     QSB_HD int dx(int i, int c) const { return i * S + c; }
     QSB_HD int dz(int i, int c) const { return i * S + n + c; }
     QSB_HD int sx(int i, int c) const { return i * S + 2 * n + c; }
@@ -59,7 +71,7 @@ struct TabView {
     QSB_HD int sg(int i) const { return i * S + 4 * n; }
     QSB_HD int ac(int i) const { return i * S + 4 * n + 1; }
 };
-QSB_HD TabView make_view(plane_t* p, size_t W, size_t w, int n) { TabView v; v.p = p; v.W = W; v.w = w; v.n = n; v.S = 4 * n + 2; return v; }
+QSB_HD TabView make_view(plane_t* p, size_t W, size_t w, int n) { TabView v; v.p = p + w; v.W = W; v.n = n; v.S = 4 * n + 2; return v; }
 
 
 // dst row (planes x0.., z0.., optional sign plane) <- src * dst on lanes m, src given in registers/local

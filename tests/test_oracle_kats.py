@@ -45,6 +45,15 @@ def test_philox_known_answers():
         [0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1]
 
 
+def test_draw_maps_two_uniforms_onto_one_philox_block():
+    seed, traj = 0x123456789ABCDEF0, 0x1_0000_0007
+    for d in (0, 1, 6, 7, (1 << 33) + 5):
+        b = d >> 1
+        o = orc.philox([traj & 0xFFFFFFFF, traj >> 32, b & 0xFFFFFFFF, b >> 32], [seed & 0xFFFFFFFF, seed >> 32])
+        lo, hi = (o[2], o[3]) if d & 1 else (o[0], o[1])
+        assert orc.draw(seed, traj, d) == float(((hi << 32) | lo) >> 11) / 2.0 ** 53
+
+
 def test_draw_is_uniform_53bit():
     us = np.array([orc.draw(0x5153, t, 7) for t in range(4000)])
     assert (us >= 0).all() and (us < 1).all()
