@@ -121,9 +121,10 @@ def lib():
     """Load libqsb200.so (building it if stale).  Raises if it cannot be loaded -- no fallback."""
     global _LIB, EXPORTS
     if _LIB is None:
-        if not os.path.exists(SO_PATH):
+        path = os.environ.get("QSB200_LIB") or SO_PATH   # QSB200_LIB: a differently tuned build of the same library
+        if path == SO_PATH and not os.path.exists(SO_PATH):
             build()
-        L = C.CDLL(SO_PATH)
+        L = C.CDLL(path)
         EXPORTS = _declare(L)
         _LIB = L
     return _LIB
