@@ -25,6 +25,7 @@ per-trajectory masks"): `apply(..., mask=m)` and `traceout(..., mask=m)` take a 
 """
 from __future__ import annotations
 
+import contextlib
 import itertools
 
 from . import ops
@@ -294,8 +295,25 @@ def apply(refs, operation, time=None, mask=None):
 
 
 # ---- observable -----------------------------------------------------------------------------------
+_OBSERVABLE_KW: dict = {}
+
+
+@contextlib.contextmanager
+def observable_options(**kw):
+    """Backend keywords (per_trajectory=True, ...) added to every observable() call inside the block, so a
+    workload driver written against the reference's signature can be asked for per-trajectory values."""
+    global _OBSERVABLE_KW
+    old, _OBSERVABLE_KW = _OBSERVABLE_KW, {**_OBSERVABLE_KW, **kw}
+    try:
+        yield
+    finally:
+        _OBSERVABLE_KW = old
+
+
 def observable(refs, obs, something=None, time=None, **kw):
     """observable(refs, obs; something, time) -- src/baseops/observable.jl:12-41."""
+    if _OBSERVABLE_KW:
+        kw = {**_OBSERVABLE_KW, **kw}
     regs, indices = _split(refs)
     if len(regs) != len(indices):
         raise ValueError("The number of registers does not match the number of slot indices.")
