@@ -181,6 +181,9 @@ int qsb_program_upload(qsb_program* prog, int64_t* bytes);
 /* info: {ops, arena planes, statistics rows, threads per block, shared bytes per block, 1 if arena in global memory,
  *        register-state ops per run summed over trajectories, draws per run} */
 int qsb_program_info(const qsb_program* prog, int64_t info[8]);
+/* SURVEY.md 8d table bytes of the recorded ops summed over trajectories: the algorithmic traffic the SAME op list
+ * accounts when every op is its own launch (the numerator of roofline.achieved for the fused launch). */
+int qsb_program_table_bytes(const qsb_program* prog, uint64_t* bytes);
 int qsb_program_free(qsb_program* prog);
 
 #ifdef __cplusplus

@@ -109,7 +109,11 @@ class Program:
     def info(self):
         a = (C.c_int64 * 8)()
         check(self.ctx.L.qsb_program_info(self.p, a))
-        return dict(zip(("ops", "planes", "stats_rows", "threads", "smem_bytes", "global_arena", "state_ops", "draws"), list(a)))
+        d = dict(zip(("ops", "planes", "stats_rows", "threads", "smem_bytes", "global_arena", "state_ops", "draws"), list(a)))
+        b = C.c_uint64()
+        check(self.ctx.L.qsb_program_table_bytes(self.p, C.byref(b)))
+        d["table_bytes"] = b.value
+        return d
 
     def free(self):
         if self.p and self.ctx.p:

@@ -23,7 +23,7 @@ struct qsb_recorder {
     std::vector<double*> stats_ptrs;
     int next_plane = 0, high = 0;
     std::multimap<int, int> free_blocks;  // size -> base
-    uint64_t ops0 = 0, draws0 = 0;        // context counters at qsb_record_begin (recording itself executes nothing)
+    uint64_t ops0 = 0, draws0 = 0, bytes0 = 0;   // context counters at qsb_record_begin (recording itself executes nothing)
     // lifetime log of every plane block, for the offline re-packing of the arena at qsb_record_end:
     // live for ops [t0, t1); sizes.back().second planes from op sizes.back().first on (in-place shrinks)
     struct Blk { int base, t0, t1; std::vector<std::pair<int, int>> sizes; int nbase; bool used; };
@@ -58,6 +58,7 @@ struct qsb_program {
     int threads, smem_bytes;
     ExecOp* h_ops;         // pinned host copy of the op list (qsb_program_upload re-sends it)
     uint64_t ops_per_run, draws_per_run, per_traj_rows;
+    uint64_t table_bytes;  // SURVEY 8d per-op algorithmic bytes summed over the recorded ops (what the per-op path would account)
 };
 
 static int rec_alloc_raw(qsb_recorder* R, int nplanes) {
@@ -221,7 +222,7 @@ extern "C" int qsb_record_begin(qsb_ctx* ctx) {
     if (!ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "null context");
     if (ctx->rec) QSB_FAIL(QSB_ERR_BAD_ARG, "already recording");
     ctx->rec = new qsb_recorder();
-    ctx->rec->ops0 = ctx->ops; ctx->rec->draws0 = ctx->draws;
+    ctx->rec->ops0 = ctx->ops; ctx->rec->draws0 = ctx->draws; ctx->rec->bytes0 = ctx->algo_bytes;
     ctx->rec_gen++;
     return QSB_OK;
 }
@@ -236,7 +237,8 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     P->nops = (int)R->ops.size(); P->nobs = (int)R->obs.size(); P->nstats = (int)R->stats_ptrs.size();
     P->planes = R->high > 0 ? R->high : 1;
     P->ops_per_run = ctx->ops - R->ops0; P->draws_per_run = ctx->draws - R->draws0;
-    ctx->ops = R->ops0; ctx->draws = R->draws0;  // counted per qsb_program_run instead
+    P->table_bytes = ctx->algo_bytes - R->bytes0;
+    ctx->ops = R->ops0; ctx->draws = R->draws0; ctx->algo_bytes = R->bytes0;  // counted per qsb_program_run instead
     for (auto& o : R->ops) if (o.per_traj) P->per_traj_rows++;
     int rc = QSB_OK;
     // Constant folding: a mixture's components are built by INIT (+FORCE...) ops whose result is the same on every
@@ -510,6 +512,12 @@ extern "C" int qsb_program_info(const qsb_program* P, int64_t info[8]) {
     if (!P || !info) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     info[0] = P->nops; info[1] = P->planes; info[2] = P->nstats; info[3] = P->threads; info[4] = P->smem_bytes; info[5] = P->arena ? 1 : 0;
     info[6] = (int64_t)P->ops_per_run; info[7] = (int64_t)P->draws_per_run;
+    return QSB_OK;
+}
+
+extern "C" int qsb_program_table_bytes(const qsb_program* P, uint64_t* bytes) {
+    if (!P || !bytes) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
+    *bytes = P->table_bytes;
     return QSB_OK;
 }
 

@@ -49,7 +49,7 @@ int qsbt_tensor2(qsb_ctx* ctx, const qsb_state* a, const qsb_state* b, qsb_state
     if (ctx->rec) {
         TabOp* o = qsb_rec_push(ctx, TOP_TENSOR); o->n = a->n; o->n2 = b->n;
         o->s[0] = st->vbase; o->s[1] = a->vbase; o->s[2] = b->vbase; o->al[0] = st->valive; o->al[1] = a->valive; o->al[2] = b->valive;
-        ctx->ops += ctx->ntraj; *out = st; return QSB_OK;
+        qsb_account(ctx, "k_tab_tensor", (uint64_t)(qsb_tab_planes(a->n) + qsb_tab_planes(b->n) + qsb_tab_planes(st->n)) * ctx->ntraj / 8); ctx->ops += ctx->ntraj; *out = st; return QSB_OK;
     }
     QSB_PRE(ctx, "k_tab_tensor");
     k_tab_tensor<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, st->alive, (const uint32_t*)a->data, (const uint32_t*)b->data, a->alive, b->alive,
@@ -94,7 +94,7 @@ int qsbt_select(qsb_ctx* ctx, const qsb_state* const* states, const double* w, i
         TabOp* o = qsb_rec_push(ctx, TOP_SELECT); o->n = st->n; o->n2 = m; o->draw = draw_id;
         o->s[0] = st->vbase; o->al[0] = st->valive;
         for (int i = 0; i < m; ++i) { o->s[1 + i] = states[i]->vbase; o->al[1 + i] = states[i]->valive; o->f[i] = a.cum[i]; }
-        ctx->ops += ctx->ntraj; *out = st; return QSB_OK;
+        qsb_account(ctx, "k_tab_select", (uint64_t)2 * qsb_tab_planes(st->n) * ctx->ntraj / 8); ctx->ops += ctx->ntraj; *out = st; return QSB_OK;
     }
     QSB_PRE(ctx, "k_tab_select");
     k_tab_select<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, st->alive, a, (size_t)ctx->nwords, qsb_tab_planes(st->n), ctx->seed, (uint64_t)ctx->traj_offset, draw_id);
@@ -154,7 +154,7 @@ int qsbt_apply(qsb_state* st, const int* idx, int k, const uint8_t* table, const
         TabOp* o = qsb_rec_push(ctx, TOP_GATE); o->n = a.n; o->k = a.k; o->q[0] = a.q[0]; o->q[1] = a.q[1]; o->lut = a.lut; o->u[0] = a.anf;
         for (int j = 0; j < 4; ++j) o->outmask[j] = a.outmask[j];
         o->s[0] = st->vbase; o->m[0] = mask ? mask->vplane : -1;
-        ctx->ops += ctx->ntraj; return QSB_OK;
+        qsb_account(ctx, "k_tab_gate", (uint64_t)2 * (2 * st->n) * (2 * k + 2) * ctx->ntraj / 8); ctx->ops += ctx->ntraj; return QSB_OK;
     }
     QSB_PRE(ctx, "k_tab_gate");
     k_tab_gate<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (size_t)ctx->nwords, a, mask ? mask->w : nullptr);
@@ -185,7 +185,7 @@ int qsbt_channel(qsb_state* st, int idx, int bg, const double* prm, double dt, u
     if (ctx->rec) {
         TabOp* o = qsb_rec_push(ctx, TOP_NOISE); o->n = a.n; o->q[0] = a.q; o->k = a.np; o->draw = draw_id; o->s[0] = st->vbase;
         for (int j = 0; j < 3; ++j) { o->f[j] = a.cum[j]; o->iv[j] = a.op[j]; }
-        ctx->ops += ctx->ntraj; ctx->draws++; return QSB_OK;
+        qsb_account(ctx, "k_tab_noise", (uint64_t)(2 * st->n) * 3 * ctx->ntraj / 8); ctx->ops += ctx->ntraj; ctx->draws++; return QSB_OK;
     }
     QSB_PRE(ctx, "k_tab_noise");
     k_tab_noise<<<tgrid(ctx), TTPB, 0, ctx->stream>>>((uint32_t*)st->data, (size_t)ctx->nwords, a, ctx->seed, (uint64_t)ctx->traj_offset, draw_id);
@@ -241,7 +241,7 @@ int qsbt_measure(qsb_state* st, int idx, int basis, uint64_t draw_id, qsb_mask* 
         o->s[0] = st->vbase; o->s[1] = st->vbase; o->al[1] = st->valive; o->m[0] = outcome2->vplane; o->m[1] = was_random ? was_random->vplane : -1;
         qsb_rec_shrink(ctx, st->vbase, qsb_tab_planes(n), qsb_tab_planes(n - 1));
         st->n = n - 1; st->bytes = qsb_state_bytes(ctx, QSB_TAB, n - 1);
-        ctx->ops += ctx->ntraj; return QSB_OK;
+        qsb_account(ctx, "k_tab_measure", (uint64_t)(qsb_tab_planes(n) + qsb_tab_planes(n - 1)) * ctx->ntraj / 8); ctx->ops += ctx->ntraj; return QSB_OK;
     }
     void* nd;
     QSB_TRY(qsb_dev_alloc(ctx, &nd, qsb_state_bytes(ctx, QSB_TAB, n - 1)));
@@ -267,7 +267,7 @@ int qsbt_ptrace(qsb_state* st, int idx) {
         TabOp* o = qsb_rec_push(ctx, TOP_PTRACE); o->n = n; o->q[0] = idx; o->s[0] = st->vbase; o->s[1] = st->vbase;
         qsb_rec_shrink(ctx, st->vbase, qsb_tab_planes(n), qsb_tab_planes(n - 1));
         st->n = n - 1; st->bytes = qsb_state_bytes(ctx, QSB_TAB, n - 1);
-        ctx->ops += ctx->ntraj; return QSB_OK;
+        qsb_account(ctx, "k_tab_ptrace", (uint64_t)(qsb_tab_planes(n) + qsb_tab_planes(n - 1)) * ctx->ntraj / 8); ctx->ops += ctx->ntraj; return QSB_OK;
     }
     void* nd;
     QSB_TRY(qsb_dev_alloc(ctx, &nd, qsb_state_bytes(ctx, QSB_TAB, n - 1)));
@@ -379,7 +379,7 @@ int qsbt_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* 
         TabOp* o = qsb_rec_push(ctx, TOP_EXPECT); o->n = n; o->s[0] = st->vbase; o->al[0] = st->valive;
         o->obs = qsb_rec_push_obs(ctx, &a, sizeof(a)); o->stats = stats_dev; o->per_traj = per_traj;
         qsb_rec_note_stats(ctx, stats_dev);
-        ctx->ops += ctx->ntraj; return QSB_OK;
+        qsb_account(ctx, "k_tab_expect", (uint64_t)n * (2 * n + 2) * ctx->ntraj / 8); ctx->ops += ctx->ntraj; return QSB_OK;
     }
     double* sd = stats_dev ? stats_dev : ((stats_host) ? ctx->stats_tmp : nullptr);
     if (sd) QSB_CUDA(cudaMemsetAsync(sd, 0, 4 * sizeof(double), ctx->stream));

@@ -301,7 +301,9 @@ _OBSERVABLE_KW: dict = {}
 @contextlib.contextmanager
 def observable_options(**kw):
     """Backend keywords (per_trajectory=True, ...) added to every observable() call inside the block, so a
-    workload driver written against the reference's signature can be asked for per-trajectory values."""
+    workload driver written against the reference's signature can be asked for per-trajectory values.
+    A callable value is called once per observable() that reaches the backend (e.g. stats_dev=next_row hands
+    every observable its own device statistics row)."""
     global _OBSERVABLE_KW
     old, _OBSERVABLE_KW = _OBSERVABLE_KW, {**_OBSERVABLE_KW, **kw}
     try:
@@ -336,6 +338,7 @@ def observable(refs, obs, something=None, time=None, **kw):
     unique, offsets = unique_staterefs_with_offsets(staterefs)
     state = unique[0].state if len(unique) == 1 else unique[0].state.subsystemcompose(*[s.state for s in unique[1:]])
     state_indices = [r.stateindices[i - 1] + offsets[id(r.staterefs[i - 1])] for r, i in zip(regs, indices)]
+    kw = {k: (v() if callable(v) else v) for k, v in kw.items()}
     return state.observable(state_indices, obs, **kw)
 
 
