@@ -153,8 +153,11 @@ int qsb_state_alloc(qsb_ctx* ctx, int kind, int n, qsb_state** out) {
     st->bytes = qsb_state_bytes(ctx, kind, n);
     st->data = nullptr; st->alive = nullptr; st->vbase = st->valive = -1; st->gen = 0;
     if (ctx->rec) {
-        if (kind != QSB_TAB) { delete st; QSB_FAIL(QSB_ERR_UNSUPPORTED, "only Clifford (tableau) states can be recorded into a program"); }
-        st->vbase = qsb_rec_alloc_planes(ctx, qsb_tab_planes(n));
+        if (kind == QSB_MCKET) { delete st; QSB_FAIL(QSB_ERR_UNSUPPORTED, "QuantumMCRepr (MCKet) states cannot be recorded into a program"); }
+        if (kind != QSB_TAB && n > QSB_DEXEC_MAXN) { delete st; QSB_FAIL(QSB_ERR_UNSUPPORTED, "dense states of more than %d subsystems cannot be recorded into a program (they do not fit on chip)", QSB_DEXEC_MAXN); }
+        if (qsb_rec_set_family(ctx, kind != QSB_TAB) != QSB_OK) { delete st; return QSB_ERR_UNSUPPORTED; }
+        // dense programs hold EVERY state as a density matrix (a ket is recorded as its projector): 4^n elements
+        st->vbase = kind == QSB_TAB ? qsb_rec_alloc_planes(ctx, qsb_tab_planes(n)) : qsb_rec_alloc(ctx, 1, 1 << (2 * n));
         st->valive = qsb_rec_alloc_planes(ctx, 1);
         st->gen = ctx->rec_gen;
         ctx->live_states->insert(st);
@@ -485,7 +488,7 @@ extern "C" int qsb_state_copy(const qsb_state* st, qsb_state** out) {
     qsb_state* c;
     QSB_TRY(qsb_state_alloc(st->ctx, st->kind, st->n, &c));
     if (st->ctx->rec) {
-        TabOp* o = qsb_rec_push(st->ctx, TOP_COPY); o->n = st->n; o->s[0] = c->vbase; o->s[1] = st->vbase; o->al[0] = c->valive; o->al[1] = st->valive;
+        TabOp* o = qsb_rec_push(st->ctx, st->kind == QSB_TAB ? TOP_COPY : DOP_COPY); o->n = st->n; o->s[0] = c->vbase; o->s[1] = st->vbase; o->al[0] = c->valive; o->al[1] = st->valive;
         *out = c; return QSB_OK;
     }
     QSB_CUDA(cudaMemcpyAsync(c->data, st->data, st->bytes, cudaMemcpyDeviceToDevice, st->ctx->stream));
@@ -497,7 +500,7 @@ extern "C" int qsb_state_free(qsb_state* st) {
     if (!st) return QSB_OK;
     st->ctx->live_states->erase(st);
     if (st->vbase >= 0) {
-        if (st->ctx->rec && st->gen == st->ctx->rec_gen) { qsb_rec_free_planes(st->ctx, st->vbase, qsb_tab_planes(st->n)); qsb_rec_free_planes(st->ctx, st->valive, 1); }
+        if (st->ctx->rec && st->gen == st->ctx->rec_gen) { qsb_rec_free(st->ctx, st->kind == QSB_TAB ? 0 : 1, st->vbase); qsb_rec_free(st->ctx, 0, st->valive); }
         delete st; return QSB_OK;
     }
     int rc = qsb_dev_free(st->ctx, st->data);

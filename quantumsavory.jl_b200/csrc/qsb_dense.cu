@@ -7,9 +7,29 @@
 // kernel is HBM bandwidth and its algorithmic bytes per trajectory are listed in DESIGN.md.
 #include <math.h>
 
+#include <vector>
+
 #include "qsb_internal.cuh"
 
 #define TPB 128
+
+// ---- record mode (dense programs, qsb_dexec.cu) --------------------------------------------------
+// Inside a recording a dense state is a block of 4^n elements in the program's element arena and is ALWAYS kept as
+// a density matrix (a ket is recorded as |psi><psi|); st->kind keeps the logical kind for the promotion rules.
+static inline uint64_t dm_elems(int n) { return (uint64_t)1 << (2 * n); }
+static int rec_const(qsb_ctx* ctx, qsb_state* st, const std::vector<double>& rho) {
+    TabOp* o = qsb_rec_push(ctx, DOP_CONST);
+    o->n = st->n; o->s[0] = st->vbase; o->al[0] = st->valive; o->obs = qsb_rec_daux(ctx, rho.data(), (int)rho.size());
+    return QSB_OK;
+}
+static std::vector<double> outer_ri(const double* psi, size_t D) {   // column-major rho[r + c D] = psi[r] conj(psi[c])
+    std::vector<double> rho(2 * D * D);
+    for (size_t c = 0; c < D; ++c) for (size_t r = 0; r < D; ++r) {
+        rho[2 * (r + c * D)] = psi[2 * r] * psi[2 * c] + psi[2 * r + 1] * psi[2 * c + 1];
+        rho[2 * (r + c * D) + 1] = psi[2 * r + 1] * psi[2 * c] - psi[2 * r] * psi[2 * c + 1];
+    }
+    return rho;
+}
 
 struct Grid2 { dim3 grid; };
 static Grid2 plan_grid(const qsb_ctx* ctx, size_t groups) {
@@ -66,6 +86,12 @@ __global__ void k_broadcast(double2* d, const double2* __restrict__ src, int64_t
 int qsbd_new(qsb_ctx* ctx, int kind, int n, qsb_state** out) {
     qsb_state* st;
     QSB_TRY(qsb_state_alloc(ctx, kind, n, &st));
+    if (ctx->rec) {
+        std::vector<double> rho(2 * dm_elems(n), 0.0);
+        rho[0] = 1.0;
+        *out = st;
+        return rec_const(ctx, st, rho);
+    }
     size_t elems = st->bytes / (ctx->npad * sizeof(double2));
     Grid2 g = plan_grid(ctx, elems);
     QSB_PRE(ctx, "k_fill0");
@@ -79,6 +105,12 @@ int qsbd_from_host(qsb_ctx* ctx, int kind, int n, const double* data, qsb_state*
     qsb_state* st;
     QSB_TRY(qsb_state_alloc(ctx, kind, n, &st));
     size_t elems = st->bytes / (ctx->npad * sizeof(double2));
+    if (ctx->rec) {
+        std::vector<double> rho = kind == QSB_DM ? std::vector<double>(data, data + 2 * dm_elems(n)) : outer_ri(data, (size_t)1 << n);
+        qsb_account(ctx, "k_broadcast", (uint64_t)elems * 16 * ctx->ntraj); ctx->ops += ctx->ntraj;
+        *out = st;
+        return rec_const(ctx, st, rho);
+    }
     void* src;
     QSB_TRY(qsb_upload(ctx, data, elems * sizeof(double2), &src));
     Grid2 g = plan_grid(ctx, elems);
@@ -108,6 +140,7 @@ __global__ void k_select(double2* d, uint32_t* alive_out, SelArgs a, int64_t npa
 }
 int qsbd_select(qsb_ctx* ctx, const qsb_state* const* states, const double* w, int m, uint64_t draw_id, qsb_state** out) {
     if (m > 8) QSB_FAIL(QSB_ERR_UNSUPPORTED, "mixtures of more than 8 states are not implemented");
+    if (ctx->rec) QSB_FAIL(QSB_ERR_UNSUPPORTED, "sampled mixtures of dense states cannot be recorded (express the mixture as a density matrix)");
     qsb_state* st;
     QSB_TRY(qsb_state_alloc(ctx, states[0]->kind, states[0]->n, &st));
     size_t elems = st->bytes / (ctx->npad * sizeof(double2));
@@ -136,6 +169,7 @@ __global__ void k_outer(double2* out, const double2* __restrict__ psi, int64_t n
 }
 int qsbd_promote_dm(qsb_state* st) {
     qsb_ctx* ctx = st->ctx;
+    if (ctx->rec) { st->kind = QSB_DM; st->bytes = qsb_state_bytes(ctx, QSB_DM, st->n); return QSB_OK; }   // already held as a dm
     size_t nbytes = qsb_state_bytes(ctx, QSB_DM, st->n);
     void* nd;
     QSB_TRY(qsb_dev_alloc(ctx, &nd, nbytes));
@@ -202,6 +236,15 @@ int qsbd_tensor2(qsb_ctx* ctx, const qsb_state* a, const qsb_state* b, qsb_state
     else if (a->kind == QSB_MCKET && b->kind == QSB_MCKET) kind = QSB_MCKET;
     else kind = QSB_KET;
     if (a->n + b->n > QSB_DENSE_MAXN) QSB_FAIL(QSB_ERR_UNSUPPORTED, "composite state would exceed %d qubits", QSB_DENSE_MAXN);
+    if (ctx->rec) {
+        qsb_state* st;
+        QSB_TRY(qsb_state_alloc(ctx, kind, a->n + b->n, &st));
+        TabOp* o = qsb_rec_push(ctx, DOP_TENSOR); o->n = a->n; o->n2 = b->n;
+        o->s[0] = st->vbase; o->s[1] = a->vbase; o->s[2] = b->vbase; o->al[0] = st->valive; o->al[1] = a->valive; o->al[2] = b->valive;
+        qsb_account(ctx, "k_tensor", (uint64_t)(qsb_state_bytes(ctx, kind, a->n) + qsb_state_bytes(ctx, kind, b->n) + st->bytes) / ctx->npad * ctx->ntraj); ctx->ops += ctx->ntraj;
+        *out = st;
+        return QSB_OK;
+    }
     qsb_state *pa = nullptr, *pb = nullptr;
     const qsb_state *xa = a, *xb = b;
     if (kind == QSB_DM && a->kind != QSB_DM) { QSB_TRY(qsb_state_copy(a, &pa)); QSB_TRY(qsbd_promote_dm(pa)); xa = pa; }
@@ -326,6 +369,13 @@ int qsbd_apply(qsb_state* st, const int* idx, int k, const double* U, const qsb_
     for (int i = 0; i < k; ++i) a.pos[i] = idx[i];
     const uint32_t* mw = mask ? mask->w : nullptr;
     int n = st->n;
+    if (ctx->rec) {
+        TabOp* o = qsb_rec_push(ctx, DOP_APPLY); o->n = n; o->k = k; o->q[0] = idx[0]; o->q[1] = k > 1 ? idx[1] : 0;
+        o->s[0] = st->vbase; o->m[0] = mask ? mask->vplane : -1; o->obs = qsb_rec_daux(ctx, U, 2 * M * M);
+        qsb_account(ctx, qsb_is_ketlike(st->kind) ? "k_apply_ket" : "k_apply_dm", (uint64_t)32 * ((uint64_t)1 << (qsb_is_ketlike(st->kind) ? n : 2 * n)) * ctx->ntraj);
+        ctx->ops += ctx->ntraj;
+        return QSB_OK;
+    }
     if (qsb_is_ketlike(st->kind)) {
         for (int i = 0; i < k; ++i) a.sorted[i] = idx[i];
         sort_ints(a.sorted, k);
@@ -537,6 +587,12 @@ int qsbd_channel(qsb_state* st, int idx, int bg, const double* prm, double dt, u
         p.a = 1; p.b = 1 - e; p.c = e; p.dd = 0; p.f = sqrt(e);
         if (tphi_inv > 0) { double pphi = 1 - exp(-dt * tphi_inv); p.f *= 1 - pphi; }
     }
+    if (ctx->rec) {
+        const double prm5[6] = {p.a, p.b, p.c, p.dd, p.f, (double)p.offdiag_only};
+        TabOp* o = qsb_rec_push(ctx, DOP_CHANNEL); o->n = n; o->q[0] = idx; o->s[0] = st->vbase; o->iv[0] = p.offdiag_only; o->obs = qsb_rec_daux(ctx, prm5, 6);
+        qsb_account(ctx, "k_channel_dm", (uint64_t)(p.offdiag_only ? 16 : 32) * ((uint64_t)1 << (2 * n)) * ctx->ntraj); ctx->ops += ctx->ntraj;
+        return QSB_OK;
+    }
     size_t groups = (size_t)1 << (2 * n - 2);
     Grid2 g = plan_grid(ctx, groups);
     QSB_PRE(ctx, "k_channel_dm");
@@ -632,6 +688,16 @@ int qsbd_measure(qsb_state* st, int idx, const double* kets, uint64_t draw_id, q
     bool ket = qsb_is_ketlike(st->kind);
     MeasArgs ma;
     for (int j = 0; j < 2; ++j) for (int a = 0; a < 2; ++a) ma.psi[j][a] = make_double2(kets[4 * j + 2 * a], kets[4 * j + 2 * a + 1]);
+    if (ctx->rec) {
+        // the qubit is projected out IN PLACE: the state keeps its base, the tail of its block is recycled
+        TabOp* o = qsb_rec_push(ctx, DOP_MEASURE); o->n = n; o->q[0] = idx; o->draw = draw_id; o->obs = qsb_rec_daux(ctx, kets, 8);
+        o->s[0] = st->vbase; o->al[0] = st->valive; o->m[0] = outcome2->vplane;
+        uint64_t e_in = ket ? ((uint64_t)1 << n) : dm_elems(n);
+        qsb_account(ctx, "k_project", (uint64_t)16 * (e_in + e_in / (ket ? 2 : 4)) * ctx->ntraj); ctx->ops += ctx->ntraj;
+        qsb_rec_shrink_to(ctx, 1, st->vbase, n > 1 ? 1 << (2 * n - 2) : 1);
+        st->n = n - 1; st->bytes = n > 1 ? qsb_state_bytes(ctx, st->kind, n - 1) : 0;
+        return QSB_OK;
+    }
     int nsplit;
     QSB_TRY(launch_rdm1(st, idx, &nsplit));
     double* scale = ctx->scratch + (size_t)nsplit * 4 * ctx->npad;
@@ -702,6 +768,15 @@ int qsbd_ptrace(qsb_state* st, int idx, uint64_t draw_id) {
         return rc;
     }
     size_t nbytes = qsb_state_bytes(ctx, QSB_DM, n - 1);
+    if (ctx->rec) {
+        TabOp* o = qsb_rec_push(ctx, DOP_PTRACE); o->n = n; o->q[0] = idx; o->s[0] = st->vbase;
+        if (st->kind == QSB_DM) qsb_account(ctx, "k_ptrace_dm", (uint64_t)16 * (dm_elems(n) / 2 + dm_elems(n - 1)) * ctx->ntraj);
+        else qsb_account(ctx, "k_ptrace_ket", (uint64_t)16 * (((uint64_t)1 << n) + dm_elems(n - 1)) * ctx->ntraj);
+        qsb_rec_shrink_to(ctx, 1, st->vbase, 1 << (2 * n - 2));
+        st->bytes = nbytes; st->n = n - 1; st->kind = QSB_DM;
+        ctx->ops += ctx->ntraj;
+        return QSB_OK;
+    }
     void* nd;
     QSB_TRY(qsb_dev_alloc(ctx, &nd, nbytes));
     size_t groups = (size_t)1 << (2 * n - 2);
@@ -836,6 +911,55 @@ int qsbd_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* 
     qsb_ctx* ctx = st->ctx;
     int n = st->n;
     bool ket = qsb_is_ketlike(st->kind);
+    if (ctx->rec) {
+        // recorded form (the state is held as a dm whatever its logical kind): iv[0] = mode, f[0..1] = global factor,
+        //   mode 0  Pauli string      u[0] = xmask, u[1] = zmask
+        //   mode 1  full projector    aux = nnz x {index, re, im}, iv[1] = nnz        value = sum_ij conj(phi_i) rho[r_i, r_j] phi_j
+        //   mode 2  k-qubit operator  aux = {pos[0..k) padded to even} ++ O (4^k complex, column-major)
+        TabOp* o = qsb_rec_push(ctx, DOP_EXPECT);
+        o->n = n; o->k = k; o->s[0] = st->vbase; o->al[0] = st->valive; o->stats = stats_dev; o->per_traj = per_traj;
+        double fr = obs_sign ? -1.0 : 1.0, fi = 0.0;
+        uint64_t algo;
+        if (obs_kind == QSB_OBS_PAULI) {
+            const uint8_t* codes = (const uint8_t*)obs;
+            int ny = 0;
+            for (int m = 0; m < k; ++m) {
+                if (codes[m] > 3) QSB_FAIL(QSB_ERR_BAD_ARG, "bad Pauli code %d", codes[m]);
+                if (codes[m] == 1 || codes[m] == 2) o->u[0] |= 1u << idx[m];
+                if (codes[m] == 3 || codes[m] == 2) o->u[1] |= 1u << idx[m];
+                if (codes[m] == 2) ++ny;
+            }
+            static const double ipw[4][2] = {{1, 0}, {0, 1}, {-1, 0}, {0, -1}};
+            fi = ipw[ny & 3][1] * fr; fr = ipw[ny & 3][0] * fr;
+            o->iv[0] = 0;
+            algo = (uint64_t)16 * ((uint64_t)1 << n) * (ket ? 2 : 1);
+        } else if (obs_kind == QSB_OBS_PROJ_KET && k == n) {
+            const double* psi = (const double*)obs;
+            std::vector<double> sp;
+            for (size_t r = 0; r < ((size_t)1 << n); ++r) {
+                size_t pp = 0;
+                for (int m = 0; m < k; ++m) pp |= ((r >> idx[m]) & 1) << m;
+                if (psi[2 * pp] != 0.0 || psi[2 * pp + 1] != 0.0) { sp.push_back((double)r); sp.push_back(psi[2 * pp]); sp.push_back(psi[2 * pp + 1]); }
+            }
+            if (sp.empty()) QSB_FAIL(QSB_ERR_BAD_ARG, "projector ket is zero");
+            o->iv[0] = 1; o->iv[1] = (int)(sp.size() / 3); o->obs = qsb_rec_daux(ctx, sp.data(), (int)sp.size());
+            algo = (uint64_t)16 * (ket ? sp.size() / 3 : (sp.size() / 3) * (sp.size() / 3));
+        } else if (obs_kind == QSB_OBS_OP || obs_kind == QSB_OBS_PROJ_KET) {
+            size_t K = (size_t)1 << k;
+            std::vector<double> pay((k + 1) / 2 * 2, 0.0);
+            for (int i = 0; i < k; ++i) pay[i] = (double)idx[i];
+            if (obs_kind == QSB_OBS_OP) pay.insert(pay.end(), (const double*)obs, (const double*)obs + 2 * K * K);
+            else { std::vector<double> O = outer_ri((const double*)obs, K); pay.insert(pay.end(), O.begin(), O.end()); }
+            o->iv[0] = 2; o->obs = qsb_rec_daux(ctx, pay.data(), (int)pay.size());
+            algo = (uint64_t)16 * (ket ? ((uint64_t)1 << n) : ((uint64_t)1 << (n + k)));
+        } else {
+            QSB_FAIL(QSB_ERR_UNSUPPORTED, "observable kind %d is not defined for dense states", obs_kind);
+        }
+        o->f[0] = fr; o->f[1] = fi;
+        qsb_rec_note_stats(ctx, stats_dev);
+        qsb_account(ctx, "k_expect", algo * ctx->ntraj); ctx->ops += ctx->ntraj;
+        return QSB_OK;
+    }
     ExpArgs a; memset(&a, 0, sizeof(a));
     a.n = n; a.k = k; a.is_ket = ket;
     size_t range;

@@ -16,21 +16,7 @@
 #include <map>
 
 #include "qsb_exec_kernel.cuh"
-
-struct qsb_recorder {
-    std::vector<TabOp> ops;
-    std::vector<TabObsArgs> obs;
-    std::vector<double*> stats_ptrs;
-    int next_plane = 0, high = 0;
-    std::multimap<int, int> free_blocks;  // size -> base
-    uint64_t ops0 = 0, draws0 = 0, bytes0 = 0;   // context counters at qsb_record_begin (recording itself executes nothing)
-    // lifetime log of every plane block, for the offline re-packing of the arena at qsb_record_end:
-    // live for ops [t0, t1); sizes.back().second planes from op sizes.back().first on (in-place shrinks)
-    struct Blk { int base, t0, t1; std::vector<std::pair<int, int>> sizes; int nbase; bool used; };
-    std::vector<Blk> blks;
-    std::map<int, int> live;              // online base -> index into blks
-    int now() const { return (int)ops.size(); }
-};
+#include "qsb_dexec.cuh"
 
 // one stochastic op of the program as the draw pass sees it
 struct DrawSpec {
@@ -47,6 +33,7 @@ struct DrawSpec {
 
 struct qsb_program {
     qsb_ctx* ctx;
+    qsb_dprogram* dprog;   // non-null: a dense program (qsb_dexec.cu); the tableau fields below are unused except d_stats
     DrawSpec* d_specs; int nspecs, nslots, slot_stride;
     uint8_t* d_aux; int naux, nfolded;   // constant tables of folded ops
     uint32_t* bits;        // [nwords][slot_stride] decision words written by k_draw_bits, read by k_tab_exec
@@ -61,7 +48,7 @@ struct qsb_program {
     uint64_t table_bytes;  // SURVEY 8d per-op algorithmic bytes summed over the recorded ops (what the per-op path would account)
 };
 
-static int rec_alloc_raw(qsb_recorder* R, int nplanes) {
+static int rec_alloc_raw(qsb_recorder* Rr, RecArena* R, int nplanes) {
     auto it = R->free_blocks.lower_bound(nplanes);
     if (it != R->free_blocks.end()) {
         int size = it->first, base = it->second;
@@ -73,11 +60,11 @@ static int rec_alloc_raw(qsb_recorder* R, int nplanes) {
     R->next_plane += nplanes;
     if (R->next_plane > R->high) {
         R->high = R->next_plane;
-        if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] op %zu: high-water %d planes (block of %d)\n", R->ops.size(), R->high, nplanes);
+        if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] op %zu: arena %d high-water %d (block of %d)\n", Rr->ops.size(), (int)(R - Rr->A), R->high, nplanes);
     }
     return base;
 }
-static void rec_free_raw(qsb_recorder* R, int base, int nplanes) {
+static void rec_free_raw(RecArena* R, int base, int nplanes) {
     // coalesce with neighbours so that large composite states can be placed again
     for (bool merged = true; merged;) {
         merged = false;
@@ -89,34 +76,57 @@ static void rec_free_raw(qsb_recorder* R, int base, int nplanes) {
     if (base + nplanes == R->next_plane) R->next_plane = base;
     else R->free_blocks.insert({nplanes, base});
 }
-int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes) {
-    qsb_recorder* R = ctx->rec;
+int qsb_rec_alloc(qsb_ctx* ctx, int arena, int nplanes) {
+    qsb_recorder* Rr = ctx->rec;
+    RecArena* R = &Rr->A[arena];
     if (nplanes <= 0) nplanes = 1;
-    int base = rec_alloc_raw(R, nplanes);
+    int base = rec_alloc_raw(Rr, R, nplanes);
     R->live[base] = (int)R->blks.size();
-    R->blks.push_back({base, R->now(), INT_MAX, {{R->now(), nplanes}}, -1, false});
+    R->blks.push_back({base, Rr->now(), INT_MAX, {{Rr->now(), nplanes}}, -1, false});
     return base;
 }
-void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes) {
+void qsb_rec_free(qsb_ctx* ctx, int arena, int base) {
     if (!ctx->rec || base < 0) return;
-    qsb_recorder* R = ctx->rec;
+    RecArena* R = &ctx->rec->A[arena];
     auto it = R->live.find(base);
     if (it == R->live.end()) return;
-    qsb_recorder::Blk& b = R->blks[it->second];
-    b.t1 = R->now();
+    RecArena::Blk& b = R->blks[it->second];
+    b.t1 = ctx->rec->now();
     rec_free_raw(R, base, b.sizes.back().second);
     R->live.erase(it);
 }
-void qsb_rec_shrink(qsb_ctx* ctx, int base, int old_planes, int new_planes) {
-    qsb_recorder* R = ctx->rec;
-    if (new_planes <= 0) new_planes = 1;   // a 0-qubit state keeps one (unused) plane, like a fresh allocation would
+void qsb_rec_shrink_to(qsb_ctx* ctx, int arena, int base, int new_planes) {
+    RecArena* R = &ctx->rec->A[arena];
+    if (new_planes <= 0) new_planes = 1;   // a 0-qubit state keeps one (unused) unit, like a fresh allocation would
     auto it = R->live.find(base);
     if (it == R->live.end()) return;
-    qsb_recorder::Blk& b = R->blks[it->second];
+    RecArena::Blk& b = R->blks[it->second];
     int cur = b.sizes.back().second;
     if (new_planes >= cur) return;
-    b.sizes.push_back({R->now(), new_planes});
+    b.sizes.push_back({ctx->rec->now(), new_planes});
     rec_free_raw(R, base + new_planes, cur - new_planes);
+}
+int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes) { return qsb_rec_alloc(ctx, 0, nplanes); }
+void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes) { (void)nplanes; qsb_rec_free(ctx, 0, base); }
+void qsb_rec_shrink(qsb_ctx* ctx, int base, int old_planes, int new_planes) { (void)old_planes; qsb_rec_shrink_to(ctx, 0, base, new_planes); }
+// a recording holds tableau states or dense states, never both (one executor per program)
+int qsb_rec_set_family(qsb_ctx* ctx, bool dense) {
+    qsb_recorder* R = ctx->rec;
+    if ((dense && R->tab) || (!dense && R->dense)) { qsb_set_error("a recorded program cannot mix tableau and dense states"); return QSB_ERR_UNSUPPORTED; }
+    if (dense) R->dense = true; else R->tab = true;
+    return QSB_OK;
+}
+// constant payload of a dense op -> offset (in doubles, 2-aligned) into the program's aux table; identical payloads share storage
+int qsb_rec_daux(qsb_ctx* ctx, const double* v, int n) {
+    qsb_recorder* R = ctx->rec;
+    std::vector<double> key(v, v + n);
+    auto it = R->daux_index.find(key);
+    if (it != R->daux_index.end()) return it->second;
+    if (R->daux.size() & 1) R->daux.push_back(0.0);
+    int off = (int)R->daux.size();
+    R->daux.insert(R->daux.end(), key.begin(), key.end());
+    R->daux_index[key] = off;
+    return off;
 }
 TabOp* qsb_rec_push(qsb_ctx* ctx, int type) {
     TabOp op;
@@ -215,6 +225,89 @@ qsb_exec_launch_fn qsb_exec_launcher(int threads) {
     }
 }
 
+// Offline re-packing of one arena.  The online allocator had to number units while the schedule was still
+// unfolding; now every block's lifetime is known, blocks only the folded ops touched can be dropped, and
+// the rest is placed big-blocks-first at the lowest offset free during its whole lifetime.  A smaller arena
+// means more resident threads per SM (the tile is [units][threads] of shared memory).
+// use_s / use_alm: which op references (state bases / alive+mask planes) live in this arena.
+static void repack_arena(qsb_recorder* R, int ai, bool use_s, bool use_alm, int& planes) {
+    typedef RecArena::Blk Blk;
+    std::vector<Blk>& B = R->A[ai].blks;
+    const int nops = (int)R->ops.size();
+    auto size_at = [](const Blk& b, int t) { int sz = b.sizes[0].second; for (auto& e : b.sizes) if (e.first <= t) sz = e.second; return sz; };
+    auto find_blk = [&](int plane, int t) -> int {
+        for (int k = 0; k < (int)B.size(); ++k) if (B[k].t0 <= t && t < B[k].t1 && plane >= B[k].base && plane < B[k].base + size_at(B[k], t)) return k;
+        return -1;
+    };
+    for (int i = 0; i < nops; ++i) {
+        const TabOp& o = R->ops[i];
+        if (o.type == TOP_NOP) continue;
+        for (int k = 0; k < 6; ++k) { if (use_s && o.s[k] >= 0) { int b = find_blk(o.s[k], i); if (b >= 0) B[b].used = true; } if (use_alm && o.al[k] >= 0) { int b = find_blk(o.al[k], i); if (b >= 0) B[b].used = true; } }
+        for (int k = 0; k < 3; ++k) if (use_alm && o.m[k] >= 0) { int b = find_blk(o.m[k], i); if (b >= 0) B[b].used = true; }
+    }
+    auto conflict = [&](const Blk& x, int xo, const Blk& y, int yo) {
+        int lo = std::max(x.t0, y.t0), hi = std::min(x.t1, y.t1);
+        if (lo >= hi) return -1;
+        // sizes only shrink: the pair overlaps at some common time iff it does at the first common time
+        // or at any later step of either staircase; check every breakpoint inside [lo, hi)
+        std::vector<int> ts{lo};
+        for (auto& e : x.sizes) if (e.first > lo && e.first < hi) ts.push_back(e.first);
+        for (auto& e : y.sizes) if (e.first > lo && e.first < hi) ts.push_back(e.first);
+        int need = -1;   // lowest offset for x that clears y at every conflicting time, -1: no conflict
+        for (int t : ts) { int xs = size_at(x, t), ys = size_at(y, t); if (xo < yo + ys && yo < xo + xs) need = std::max(need, yo + ys); }
+        return need;
+    };
+    std::vector<int> order;
+    for (int k = 0; k < (int)B.size(); ++k) if (B[k].used) order.push_back(k);
+    // several placement orders, keep the tightest: long-lived blocks first (temporaries stack on top),
+    // big blocks first, and allocation order
+    auto life = [&](int k) { return (long)std::min(B[k].t1, nops) - B[k].t0; };
+    auto place = [&](const std::vector<int>& ord, std::vector<int>& nb) {
+        std::vector<int> placed;
+        int pk = 0;
+        for (int k : ord) {
+            int off = 0;
+            for (bool moved = true; moved;) {
+                moved = false;
+                for (int j : placed) { int need = conflict(B[k], off, B[j], nb[j]); if (need >= 0) { off = need; moved = true; } }
+            }
+            nb[k] = off; placed.push_back(k);
+            pk = std::max(pk, off + B[k].sizes[0].second);
+        }
+        return pk;
+    };
+    int peak = INT_MAX;
+    for (int variant = 0; variant < 4; ++variant) {
+        std::vector<int> ord = order, nb(B.size(), -1);
+        if (variant == 0) std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return life(a) > life(b); });
+        if (variant == 1) std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return B[a].sizes[0].second > B[b].sizes[0].second; });
+        if (variant == 2) std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return life(a) * B[a].sizes[0].second > life(b) * B[b].sizes[0].second; });
+        int pk = place(ord, nb);
+        if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] packing order %d: %d planes\n", variant, pk);
+        if (pk < peak) { peak = pk; for (int k : order) B[k].nbase = nb[k]; }
+    }
+    if (order.empty()) peak = 0;
+    if (peak > 0 && peak <= planes && !getenv("QSB_NO_REPACK")) {
+        auto remap = [&](int& plane, int t) { if (plane < 0) return; int b = find_blk(plane, t); if (b >= 0 && B[b].used) plane = plane - B[b].base + B[b].nbase; };
+        for (int i = 0; i < nops; ++i) {
+            TabOp& o = R->ops[i];
+            if (o.type == TOP_NOP) continue;
+            for (int k = 0; k < 6; ++k) { if (use_s) remap(o.s[k], i); if (use_alm) remap(o.al[k], i); }
+            for (int k = 0; k < 3; ++k) if (use_alm) remap(o.m[k], i);
+        }
+        if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] arena re-packed: %d -> %d planes (%zu blocks)\n", planes, peak, order.size());
+        planes = peak;
+    } else if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] arena NOT re-packed: online %d planes, offline %d\n", planes, peak);
+    if (getenv("QSB_REC_TRACE") && nops > 0) {
+        int best = 0, bt = 0;
+        for (int t = 0; t < nops; ++t) { int sum = 0; for (int k : order) if (B[k].t0 <= t && t < B[k].t1) sum += size_at(B[k], t); if (sum > best) { best = sum; bt = t; } }
+        fprintf(stderr, "[rec] live-plane lower bound %d at op %d (type %d):", best, bt, R->ops[bt].type);
+        for (int k : order) if (B[k].t0 <= bt && bt < B[k].t1) fprintf(stderr, " %d[%d,%d)", size_at(B[k], bt), B[k].t0, B[k].t1 == INT_MAX ? -1 : B[k].t1);
+        fprintf(stderr, "\n");
+    }
+
+}
+
 // ---------------------------------------------------------------------------------------------
 // C-ABI: record / run
 // ---------------------------------------------------------------------------------------------
@@ -235,12 +328,31 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     memset(P, 0, sizeof(*P));
     P->ctx = ctx;
     P->nops = (int)R->ops.size(); P->nobs = (int)R->obs.size(); P->nstats = (int)R->stats_ptrs.size();
-    P->planes = R->high > 0 ? R->high : 1;
+    P->planes = R->A[0].high > 0 ? R->A[0].high : 1;
     P->ops_per_run = ctx->ops - R->ops0; P->draws_per_run = ctx->draws - R->draws0;
     P->table_bytes = ctx->algo_bytes - R->bytes0;
     ctx->ops = R->ops0; ctx->draws = R->draws0; ctx->algo_bytes = R->bytes0;  // counted per qsb_program_run instead
     for (auto& o : R->ops) if (o.per_traj) P->per_traj_rows++;
     int rc = QSB_OK;
+    if (R->dense) {
+        int nmasks = R->A[0].high > 0 ? R->A[0].high : 1, elems = R->A[1].high > 0 ? R->A[1].high : 1;
+        repack_arena(R, 0, false, true, nmasks);
+        repack_arena(R, 1, true, false, elems);
+        rc = qsb_dexec_build(ctx, R, elems, nmasks, &P->dprog);
+        if (rc == QSB_OK) {
+            rc = qsb_dev_alloc(ctx, (void**)&P->d_stats, R->stats_ptrs.empty() ? 16 : R->stats_ptrs.size() * sizeof(double*));
+            if (rc == QSB_OK && !R->stats_ptrs.empty()) {
+                if (cudaMemcpyAsync(P->d_stats, R->stats_ptrs.data(), R->stats_ptrs.size() * sizeof(double*), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess ||
+                    cudaStreamSynchronize(ctx->stream) != cudaSuccess) { qsb_set_error("program upload failed"); rc = QSB_ERR_CUDA; }
+            }
+        }
+        P->planes = elems; P->threads = QSB_DEXEC_THREADS;
+        delete R;
+        ctx->rec = nullptr;
+        if (rc != QSB_OK) { if (P->dprog) qsb_dexec_free(P->dprog); if (P->d_stats) qsb_dev_free(ctx, P->d_stats); delete P; return rc; }
+        *out = P;
+        return QSB_OK;
+    }
     // Constant folding: a mixture's components are built by INIT (+FORCE...) ops whose result is the same on every
     // lane.  Evaluate those on the host (the tableau core is host-callable), drop them, and let the SELECT pick each
     // plane from a per-plane table of "which components have this bit set" instead of reading component tableaux.
@@ -283,86 +395,7 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
                 it = used ? pend.erase(it) : std::next(it);
             }
         }
-        // Offline re-packing of the arena.  The online allocator had to number planes while the schedule was still
-        // unfolding; now every block's lifetime is known, blocks only the folded ops touched can be dropped, and
-        // the rest is placed big-blocks-first at the lowest offset free during its whole lifetime.  A smaller arena
-        // means more resident threads per SM (the tile is [planes][threads] of shared memory).
-        {
-            typedef qsb_recorder::Blk Blk;
-            std::vector<Blk>& B = R->blks;
-            const int nops = (int)R->ops.size();
-            auto size_at = [](const Blk& b, int t) { int sz = b.sizes[0].second; for (auto& e : b.sizes) if (e.first <= t) sz = e.second; return sz; };
-            auto find_blk = [&](int plane, int t) -> int {
-                for (int k = 0; k < (int)B.size(); ++k) if (B[k].t0 <= t && t < B[k].t1 && plane >= B[k].base && plane < B[k].base + size_at(B[k], t)) return k;
-                return -1;
-            };
-            for (int i = 0; i < nops; ++i) {
-                const TabOp& o = R->ops[i];
-                if (o.type == TOP_NOP) continue;
-                for (int k = 0; k < 6; ++k) { if (o.s[k] >= 0) { int b = find_blk(o.s[k], i); if (b >= 0) B[b].used = true; } if (o.al[k] >= 0) { int b = find_blk(o.al[k], i); if (b >= 0) B[b].used = true; } }
-                for (int k = 0; k < 3; ++k) if (o.m[k] >= 0) { int b = find_blk(o.m[k], i); if (b >= 0) B[b].used = true; }
-            }
-            auto conflict = [&](const Blk& x, int xo, const Blk& y, int yo) {
-                int lo = std::max(x.t0, y.t0), hi = std::min(x.t1, y.t1);
-                if (lo >= hi) return -1;
-                // sizes only shrink: the pair overlaps at some common time iff it does at the first common time
-                // or at any later step of either staircase; check every breakpoint inside [lo, hi)
-                std::vector<int> ts{lo};
-                for (auto& e : x.sizes) if (e.first > lo && e.first < hi) ts.push_back(e.first);
-                for (auto& e : y.sizes) if (e.first > lo && e.first < hi) ts.push_back(e.first);
-                int need = -1;   // lowest offset for x that clears y at every conflicting time, -1: no conflict
-                for (int t : ts) { int xs = size_at(x, t), ys = size_at(y, t); if (xo < yo + ys && yo < xo + xs) need = std::max(need, yo + ys); }
-                return need;
-            };
-            std::vector<int> order;
-            for (int k = 0; k < (int)B.size(); ++k) if (B[k].used) order.push_back(k);
-            // several placement orders, keep the tightest: long-lived blocks first (temporaries stack on top),
-            // big blocks first, and allocation order
-            auto life = [&](int k) { return (long)std::min(B[k].t1, nops) - B[k].t0; };
-            auto place = [&](const std::vector<int>& ord, std::vector<int>& nb) {
-                std::vector<int> placed;
-                int pk = 0;
-                for (int k : ord) {
-                    int off = 0;
-                    for (bool moved = true; moved;) {
-                        moved = false;
-                        for (int j : placed) { int need = conflict(B[k], off, B[j], nb[j]); if (need >= 0) { off = need; moved = true; } }
-                    }
-                    nb[k] = off; placed.push_back(k);
-                    pk = std::max(pk, off + B[k].sizes[0].second);
-                }
-                return pk;
-            };
-            int peak = INT_MAX;
-            for (int variant = 0; variant < 4; ++variant) {
-                std::vector<int> ord = order, nb(B.size(), -1);
-                if (variant == 0) std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return life(a) > life(b); });
-                if (variant == 1) std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return B[a].sizes[0].second > B[b].sizes[0].second; });
-                if (variant == 2) std::stable_sort(ord.begin(), ord.end(), [&](int a, int b) { return life(a) * B[a].sizes[0].second > life(b) * B[b].sizes[0].second; });
-                int pk = place(ord, nb);
-                if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] packing order %d: %d planes\n", variant, pk);
-                if (pk < peak) { peak = pk; for (int k : order) B[k].nbase = nb[k]; }
-            }
-            if (order.empty()) peak = 0;
-            if (peak > 0 && peak <= P->planes && !getenv("QSB_NO_REPACK")) {
-                auto remap = [&](int& plane, int t) { if (plane < 0) return; int b = find_blk(plane, t); if (b >= 0 && B[b].used) plane = plane - B[b].base + B[b].nbase; };
-                for (int i = 0; i < nops; ++i) {
-                    TabOp& o = R->ops[i];
-                    if (o.type == TOP_NOP) continue;
-                    for (int k = 0; k < 6; ++k) { remap(o.s[k], i); remap(o.al[k], i); }
-                    for (int k = 0; k < 3; ++k) remap(o.m[k], i);
-                }
-                if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] arena re-packed: %d -> %d planes (%zu blocks)\n", P->planes, peak, order.size());
-                P->planes = peak;
-            } else if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] arena NOT re-packed: online %d planes, offline %d\n", P->planes, peak);
-            if (getenv("QSB_REC_TRACE")) {
-                int best = 0, bt = 0;
-                for (int t = 0; t < nops; ++t) { int sum = 0; for (int k : order) if (B[k].t0 <= t && t < B[k].t1) sum += size_at(B[k], t); if (sum > best) { best = sum; bt = t; } }
-                fprintf(stderr, "[rec] live-plane lower bound %d at op %d (type %d):", best, bt, R->ops[bt].type);
-                for (int k : order) if (B[k].t0 <= bt && bt < B[k].t1) fprintf(stderr, " %d[%d,%d)", size_at(B[k], bt), B[k].t0, B[k].t1 == INT_MAX ? -1 : B[k].t1);
-                fprintf(stderr, "\n");
-            }
-        }
+        repack_arena(R, 0, true, true, P->planes);
         // drop the NOPs
         std::vector<TabOp> kept;
         for (auto& o : R->ops) if (o.type != TOP_NOP) kept.push_back(o);
@@ -468,6 +501,11 @@ extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t dra
         k_zero_stats<<<(P->nstats + 127) / 128, 128, 0, ctx->stream>>>(P->d_stats, P->nstats);
         QSB_LAUNCH_CHECK(ctx);
     }
+    if (P->dprog) {
+        QSB_TRY(qsb_dexec_run(P->dprog, traj_shift, draw_base));
+        ctx->ops += P->ops_per_run; ctx->draws += P->draws_per_run;
+        return QSB_OK;
+    }
     ExecArgs a;
     a.ops = P->d_ops; a.nops = P->nops; a.obs = P->d_obs; a.aux = P->d_aux; a.arena = P->arena; a.valid = (const plane_t*)ctx->valid; a.W = (size_t)ctx->nwords * (32 / QSB_LANES);
     a.seed = ctx->seed; a.traj0 = (uint64_t)ctx->traj_offset + traj_shift; a.draw_base = draw_base;
@@ -500,6 +538,7 @@ extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t dra
 // program's only host-side input, so an end-to-end timing that starts from host buffers includes this copy.
 extern "C" int qsb_program_upload(qsb_program* P, int64_t* bytes) {
     if (!P) QSB_FAIL(QSB_ERR_BAD_ARG, "null program");
+    if (P->dprog) return qsb_dexec_upload(P->dprog, bytes);
     size_t b = (size_t)P->nops * sizeof(ExecOp);
     if (b) QSB_CUDA(cudaMemcpyAsync(P->d_ops, P->h_ops, b, cudaMemcpyHostToDevice, P->ctx->stream));
     if (bytes) *bytes = (int64_t)b;
@@ -511,7 +550,8 @@ extern "C" int qsb_program_upload(qsb_program* P, int64_t* bytes) {
 extern "C" int qsb_program_info(const qsb_program* P, int64_t info[8]) {
     if (!P || !info) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     info[0] = P->nops; info[1] = P->planes; info[2] = P->nstats; info[3] = P->threads; info[4] = P->smem_bytes; info[5] = P->arena ? 1 : 0;
-    info[6] = (int64_t)P->ops_per_run; info[7] = (int64_t)P->draws_per_run;
+    if (P->dprog) qsb_dexec_info(P->dprog, info);
+    info[2] = P->nstats; info[6] = (int64_t)P->ops_per_run; info[7] = (int64_t)P->draws_per_run;
     return QSB_OK;
 }
 
@@ -524,6 +564,7 @@ extern "C" int qsb_program_table_bytes(const qsb_program* P, uint64_t* bytes) {
 extern "C" int qsb_program_free(qsb_program* P) {
     if (!P) return QSB_OK;
     qsb_ctx* ctx = P->ctx;
+    if (P->dprog) { qsb_dexec_free(P->dprog); qsb_dev_free(ctx, P->d_stats); delete P; return QSB_OK; }
     qsb_dev_free(ctx, P->d_ops); qsb_dev_free(ctx, P->d_obs); qsb_dev_free(ctx, P->d_stats);
     qsb_dev_free(ctx, P->d_specs); qsb_dev_free(ctx, P->bits); qsb_dev_free(ctx, P->d_aux);
     if (P->arena) qsb_dev_free(ctx, P->arena);

@@ -131,7 +131,10 @@ int qsbt_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* 
 // ---- recorded programs (qsb_exec.cu): tableau op lists executed by ONE fused launch ----------------
 enum { TOP_INIT, TOP_TENSOR, TOP_SELECT, TOP_COPY, TOP_GATE, TOP_NOISE, TOP_MEASURE, TOP_PTRACE, TOP_FORCE, TOP_EXPECT,
        TOP_MASK_FILL, TOP_MASK_LOGIC, TOP_MASK_RANDOM, TOP_KILL, TOP_ALIVE_COPY,
-       TOP_NOP, TOP_SELECT_CONST /* produced by constant folding at qsb_record_end */ };
+       TOP_NOP, TOP_SELECT_CONST /* produced by constant folding at qsb_record_end */,
+       // dense programs (qsb_dexec.cu): every state is held as a density matrix of 4^n elements in the element arena
+       DOP_CONST, DOP_TENSOR, DOP_COPY, DOP_APPLY, DOP_CHANNEL, DOP_MEASURE, DOP_PTRACE, DOP_EXPECT };
+#define QSB_DEXEC_MAXN 5   /* largest state of a dense program: 4^5 elements per trajectory */
 struct TabOp {
     int type, n, n2, k;
     int s[6];       // state base planes (s[0] is the destination where there is one)
@@ -148,6 +151,12 @@ struct TabOp {
     int obs;            // index into the program's TabObsArgs table
     int dslot;          // first decision-word slot of a stochastic op (filled at qsb_record_end)
 };
+// arena 0: bit planes (tableaux, masks, alive bits); arena 1: matrix elements of dense programs
+int qsb_rec_alloc(qsb_ctx* ctx, int arena, int units);
+void qsb_rec_free(qsb_ctx* ctx, int arena, int base);
+void qsb_rec_shrink_to(qsb_ctx* ctx, int arena, int base, int new_units);   // keep the head of a block, recycle its tail
+int qsb_rec_set_family(qsb_ctx* ctx, bool dense);                            // a program is all-tableau or all-dense
+int qsb_rec_daux(qsb_ctx* ctx, const double* v, int n);                      // constant payload -> offset into the aux table
 int qsb_rec_alloc_planes(qsb_ctx* ctx, int nplanes);
 void qsb_rec_free_planes(qsb_ctx* ctx, int base, int nplanes);
 void qsb_rec_shrink(qsb_ctx* ctx, int base, int old_planes, int new_planes);  // keep the head of a block, recycle its tail

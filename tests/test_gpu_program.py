@@ -80,7 +80,7 @@ def test_program_matches_per_op_path(ntraj):
     prog.free(); ctx.close(); ctx2.close()
 
 
-def test_recording_refuses_host_visible_calls_and_dense_states():
+def test_recording_refuses_host_visible_calls_and_trajectory_kets():
     from qsb200 import ops
     from qsb200._lib import MethodError, QsbError
     from qsb200.backend import BatchContext, CudaBatchRepr
@@ -91,7 +91,11 @@ def test_recording_refuses_host_visible_calls_and_dense_states():
             outside.apply([1], ops.X)               # handle from outside the recording
     with pytest.raises(MethodError):
         with ctx.record():
-            CudaBatchRepr(ctx, "qo").newstate()     # dense kinds are not recordable in this round
+            CudaBatchRepr(ctx, "mc").newstate()     # QuantumMCRepr trajectory kets are not recordable
+    with pytest.raises(MethodError):
+        with ctx.record():
+            CudaBatchRepr(ctx, "clifford").newstate()
+            CudaBatchRepr(ctx, "qo").newstate()     # one program = one family of states (tableau or dense)
     with pytest.raises(MethodError):
         with ctx.record():
             s = CudaBatchRepr(ctx, "clifford").newstate()
