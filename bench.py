@@ -91,7 +91,7 @@ def wl_grid(make_repr, formalism, record):
 WORKLOADS = {
     "firstgenrepeater_clifford": dict(fn=wl_fgr, formalism="clifford", ntraj=1_000_000,
                                       desc="examples/firstgenrepeater_lowlevel, sizes [2,3,4,3,2], F=0.97, CliffordRepr, Depolarization(100), t=0:0.2:25"),
-    "firstgenrepeater_dm": dict(fn=wl_fgr, formalism="qo", ntraj=1_000_000,
+    "firstgenrepeater_dm": dict(fn=wl_fgr, formalism="qo", ntraj=1_000_000, program=True,
                                 desc="examples/firstgenrepeater_lowlevel, sizes [2,3,4,3,2], F=0.97, QuantumOpticsRepr dm, T1T2Noise(1000,100), t=0:0.2:25"),
     "ghz_sensors_dm": dict(fn=wl_ghz, formalism="qo", ntraj=16384,
                            desc="examples/distributed_ghz_sensors F-TMBL trial, S=4 all links up (peak 8-qubit dm = 1 MiB per trajectory), F=0.99, Depolarization(1.0); "
@@ -349,17 +349,17 @@ def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, pr
             # divided by the run's device time (both kernels).  What the run really has to move through HBM is far
             # less (decision words, op list, statistics): reported as fused_hbm_*.
             info = out["program"]
-            fused = [r for r in rows if r["kernel"] in ("k_tab_exec", "k_draw_bits")]
+            fused = [r for r in rows if r["kernel"] in ("k_tab_exec", "k_draw_bits", "k_dense_exec")]
             sec = sum(r["ms"] for r in fused) * 1e-3 / max(1, fused[0]["launches"])
             hbm = sum(r["algo_bytes"] for r in fused) / max(1, fused[0]["launches"])
             gbs = info["table_bytes"] / sec / 1e9
-            out["roofline"] = {"bound": "hbm", "kernel": "k_draw_bits+k_tab_exec", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+            out["roofline"] = {"bound": "hbm", "kernel": "+".join(sorted(r["kernel"] for r in fused)), "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
                                "traffic": None, "peak_source": which, "algo_bytes_per_launch": info["table_bytes"], "us_per_launch": sec * 1e6,
                                "share_of_step": sum(r["share"] for r in fused),
                                "fused_hbm_bytes_per_launch": hbm, "fused_hbm_gbs": hbm / sec / 1e9,
                                "note": ("algorithmic bytes = SURVEY 8d table bytes of the recorded ops (per-op accounting of the same op list); the fused run keeps "
-                                        "the tableaux in shared memory, so its compulsory HBM traffic is only fused_hbm_bytes_per_launch and the kernels are "
-                                        "integer-ALU / shared-memory bound (Philox4x32-10 draws + bit-sliced row logic), see alu"),
+                                        "the states in shared memory, so its compulsory HBM traffic is only fused_hbm_bytes_per_launch and the kernels are "
+                                        "bound on chip (Clifford: Philox4x32-10 draws + bit-sliced row logic; dense: fp64 pipe + shared-memory bandwidth), see alu"),
                                "alu": {"philox_draws_per_s": info["draws"] * ntraj / sec, "state_ops_per_s": info["state_ops"] / sec,
                                        "draws_per_trajectory": info["draws"], "recorded_ops": info["ops"]}}
     ctx.close()
@@ -414,9 +414,7 @@ def main():
     import torch.distributed as dist
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    mode = args.mode if args.mode != "auto" else ("program" if w["formalism"] == "clifford" else "per_op")
-    if mode == "program" and w["formalism"] != "clifford":
-        raise SystemExit("only Clifford workloads can be recorded into a fused program in this round")
+    mode = args.mode if args.mode != "auto" else ("program" if w.get("program", w["formalism"] == "clifford") else "per_op")
     config["mode"] = ("recorded program: host schedule captured once (untimed, program.record_ms), every step = ONE fused launch over a fresh batch of trajectories"
                       if mode == "program" else "per-op: host schedule re-run every step, one launch per backend call")
     main_res = run_gpu_workload(args.workload, ntraj, args.steps, args.warmup, rank, world, local_rank, mode=mode)
@@ -432,7 +430,7 @@ def main():
         for name in [x for x in args.extras.split(",") if x and x != args.workload]:
             try:
                 r = run_gpu_workload(name, WORKLOADS[name]["ntraj"], max(2, min(args.steps, 3)), 3, 0, 1, local_rank,
-                                     mode="program" if WORKLOADS[name]["formalism"] == "clifford" else "per_op")
+                                     mode="program" if WORKLOADS[name].get("program", WORKLOADS[name]["formalism"] == "clifford") else "per_op")
                 extra[name] = {k: r[k] for k in keep if k in r}
                 extra[name]["state_ops_per_sec"] = r["ops_per_step"] / (r["dev_ms_per_step"] * 1e-3)
             except Exception as e:  # an extra must never take the headline down

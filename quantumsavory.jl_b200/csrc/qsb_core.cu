@@ -151,7 +151,7 @@ int qsb_state_alloc(qsb_ctx* ctx, int kind, int n, qsb_state** out) {
     qsb_state* st = new qsb_state();
     st->ctx = ctx; st->kind = kind; st->n = n;
     st->bytes = qsb_state_bytes(ctx, kind, n);
-    st->data = nullptr; st->alive = nullptr; st->vbase = st->valive = -1; st->gen = 0;
+    st->data = nullptr; st->alive = nullptr; st->vbase = st->valive = -1; st->gen = 0; st->vcap = 0;
     if (ctx->rec) {
         if (kind == QSB_MCKET) { delete st; QSB_FAIL(QSB_ERR_UNSUPPORTED, "QuantumMCRepr (MCKet) states cannot be recorded into a program"); }
         if (kind != QSB_TAB && n > QSB_DEXEC_MAXN) { delete st; QSB_FAIL(QSB_ERR_UNSUPPORTED, "dense states of more than %d subsystems cannot be recorded into a program (they do not fit on chip)", QSB_DEXEC_MAXN); }
@@ -159,6 +159,7 @@ int qsb_state_alloc(qsb_ctx* ctx, int kind, int n, qsb_state** out) {
         // dense programs hold EVERY state as a density matrix (a ket is recorded as its projector): 4^n elements
         st->vbase = kind == QSB_TAB ? qsb_rec_alloc_planes(ctx, qsb_tab_planes(n)) : qsb_rec_alloc(ctx, 1, 1 << (2 * n));
         st->valive = qsb_rec_alloc_planes(ctx, 1);
+        st->vcap = kind == QSB_TAB ? 0 : 1 << (2 * n);
         st->gen = ctx->rec_gen;
         ctx->live_states->insert(st);
         *out = st;

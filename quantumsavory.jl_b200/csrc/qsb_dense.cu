@@ -22,6 +22,17 @@ static int rec_const(qsb_ctx* ctx, qsb_state* st, const std::vector<double>& rho
     o->n = st->n; o->s[0] = st->vbase; o->al[0] = st->valive; o->obs = qsb_rec_daux(ctx, rho.data(), (int)rho.size());
     return QSB_OK;
 }
+// After an in-place shrink a small state would keep sitting at the base of the big block it was projected out of (the
+// pair left by a swap at the base of the 256-element composite), fragmenting the arena for as long as it lives.  Move it
+// to a block of its own size: a 16-element copy in shared memory buys a much smaller arena (more trajectories per SM).
+static void rec_relocate_small(qsb_ctx* ctx, qsb_state* st) {
+    const int need = st->n >= 1 ? 1 << (2 * st->n) : 1;
+    if (st->n < 1 || st->n > 2 || st->vcap <= need) return;
+    const int nb = qsb_rec_alloc(ctx, 1, need);
+    TabOp* o = qsb_rec_push(ctx, DOP_COPY); o->n = st->n; o->s[0] = nb; o->s[1] = st->vbase; o->al[0] = st->valive; o->al[1] = st->valive;
+    qsb_rec_free(ctx, 1, st->vbase);
+    st->vbase = nb; st->vcap = need;
+}
 static std::vector<double> outer_ri(const double* psi, size_t D) {   // column-major rho[r + c D] = psi[r] conj(psi[c])
     std::vector<double> rho(2 * D * D);
     for (size_t c = 0; c < D; ++c) for (size_t r = 0; r < D; ++r) {
@@ -696,6 +707,7 @@ int qsbd_measure(qsb_state* st, int idx, const double* kets, uint64_t draw_id, q
         qsb_account(ctx, "k_project", (uint64_t)16 * (e_in + e_in / (ket ? 2 : 4)) * ctx->ntraj); ctx->ops += ctx->ntraj;
         qsb_rec_shrink_to(ctx, 1, st->vbase, n > 1 ? 1 << (2 * n - 2) : 1);
         st->n = n - 1; st->bytes = n > 1 ? qsb_state_bytes(ctx, st->kind, n - 1) : 0;
+        rec_relocate_small(ctx, st);
         return QSB_OK;
     }
     int nsplit;
@@ -775,6 +787,7 @@ int qsbd_ptrace(qsb_state* st, int idx, uint64_t draw_id) {
         qsb_rec_shrink_to(ctx, 1, st->vbase, 1 << (2 * n - 2));
         st->bytes = nbytes; st->n = n - 1; st->kind = QSB_DM;
         ctx->ops += ctx->ntraj;
+        rec_relocate_small(ctx, st);
         return QSB_OK;
     }
     void* nd;

@@ -88,8 +88,8 @@ __device__ __forceinline__ void d_apply(const DTile& t, const DExecOp& op, const
 // closed-form single-qubit channel on the 2x2 blocks of qubit q (coefficients a, b, c, dd, f; see qsb_dense.cu)
 __device__ __forceinline__ void d_channel(const DTile& t, const DExecOp& op, const double* __restrict__ aux) {
     const double* p = aux + op.aux;
-    const double a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), dd = __ldg(p + 3), f = __ldg(p + 4);
-    const bool offdiag = __ldg(p + 5) != 0.0;
+    const double a = p[0], b = p[1], c = p[2], dd = p[3], f = p[4];
+    const bool offdiag = p[5] != 0.0;
     const int n = op.n, q = op.q[0], base0 = op.s[0];
     const int rbit = 1 << q, cbit = 1 << (q + n), groups = 1 << (2 * n - 2);
     for (int g = t.grp; g < groups; g += t.G) {
@@ -134,7 +134,7 @@ __device__ __forceinline__ void d_measure_decide(const DTile& t, const DExecOp& 
     double P[2];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-        const double2 a0 = make_double2(__ldg(kp + 4 * j), __ldg(kp + 4 * j + 1)), a1 = make_double2(__ldg(kp + 4 * j + 2), __ldg(kp + 4 * j + 3));
+        const double2 a0 = make_double2(kp[4 * j], kp[4 * j + 1]), a1 = make_double2(kp[4 * j + 2], kp[4 * j + 3]);
         const double2 x = cconjmul(a0, a1);
         P[j] = (a0.x * a0.x + a0.y * a0.y) * m00 + (a1.x * a1.x + a1.y * a1.y) * m11 + 2.0 * (x.x * mre - x.y * mim);
     }
@@ -217,11 +217,11 @@ __device__ __forceinline__ void d_expect(const DTile& t, const DExecOp& op, cons
         const double* sp = a.aux + op.aux;
         const int nnz = op.nnz;
         for (int i = 0; i < nnz; ++i) {
-            const int ri = (int)__ldg(sp + 3 * i);
-            const double2 ai = make_double2(__ldg(sp + 3 * i + 1), __ldg(sp + 3 * i + 2));
+            const int ri = (int)sp[3 * i];
+            const double2 ai = make_double2(sp[3 * i + 1], sp[3 * i + 2]);
             for (int j = 0; j < nnz; ++j) {
-                const int rj = (int)__ldg(sp + 3 * j);
-                const double2 aj = make_double2(__ldg(sp + 3 * j + 1), __ldg(sp + 3 * j + 2));
+                const int rj = (int)sp[3 * j];
+                const double2 aj = make_double2(sp[3 * j + 1], sp[3 * j + 2]);
                 const double2 v = cmul(cconjmul(ai, t.at(s0, ri + (rj << n))), aj);
                 re += v.x; im += v.y;
             }
@@ -231,7 +231,7 @@ __device__ __forceinline__ void d_expect(const DTile& t, const DExecOp& op, cons
         const double* pp = a.aux + op.aux;
         const double2* O = reinterpret_cast<const double2*>(pp + (k + 1) / 2 * 2);
         int pos[QSB_DEXEC_MAXN], sorted[QSB_DEXEC_MAXN];
-        for (int i = 0; i < k; ++i) { pos[i] = (int)__ldg(pp + i); sorted[i] = pos[i]; }
+        for (int i = 0; i < k; ++i) { pos[i] = (int)pp[i]; sorted[i] = pos[i]; }
         for (int i = 1; i < k; ++i) for (int j = i; j > 0 && sorted[j] < sorted[j - 1]; --j) { const int x = sorted[j]; sorted[j] = sorted[j - 1]; sorted[j - 1] = x; }
         for (int g = 0; g < (1 << (n - k)); ++g) {
             int b = g;
@@ -240,7 +240,7 @@ __device__ __forceinline__ void d_expect(const DTile& t, const DExecOp& op, cons
                 int ei = b;
                 for (int c = 0; c < k; ++c) ei |= ((i >> c) & 1) << pos[c];
                 for (int j = 0; j < K; ++j) {
-                    const double2 o = __ldg(O + i + j * K);
+                    const double2 o = O[i + j * K];
                     if (o.x == 0.0 && o.y == 0.0) continue;
                     int ej = b;
                     for (int c = 0; c < k; ++c) ej |= ((j >> c) & 1) << pos[c];
@@ -268,20 +268,26 @@ __device__ __forceinline__ void d_expect(const DTile& t, const DExecOp& op, cons
     }
 }
 
-// MINB: blocks per SM the register allocation must allow (1: up to 255 registers, for programs whose arena fills an SM;
-// 2: 128 registers, for small arenas where two or more tiles share an SM)
-template <int MINB>
-__global__ void __launch_bounds__(QSB_DEXEC_THREADS, MINB) k_dense_exec(DExecArgs a) {
+// THREADS x MINB: block size and the blocks per SM the register allocation must allow -- 256x1 (up to 255 registers) for
+// programs whose arena fills an SM, 256x2 and 128x4 (128 registers) for smaller arenas where several tiles share an SM.
+template <int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_dense_exec(DExecArgs a0) {
     extern __shared__ double2 dsm[];
     __shared__ DExecOp sops[QSB_DEXEC_CHUNK];
+    DExecArgs a = a0;
     DTile t;
-    t.logT = a.logT; t.T = 1 << a.logT; t.G = QSB_DEXEC_THREADS >> a.logT;
+    t.logT = a.logT; t.T = 1 << a.logT; t.G = THREADS >> a.logT;
     t.lane = threadIdx.x & (t.T - 1); t.grp = threadIdx.x >> a.logT;
     t.gshift = (int)(threadIdx.x & 31u) & ~(t.T - 1);
     t.gmask = t.T == 32 ? 0xffffffffu : (((1u << t.T) - 1u) << t.gshift);
     t.arena = dsm;
     t.scr = reinterpret_cast<double*>(dsm + (size_t)a.elems * t.T);
     t.masks = reinterpret_cast<uint32_t*>(t.scr + 2 * t.T);
+    if (a.aux_smem) {   // the constants of every op (gate matrices, channel coefficients, kets) next to the arena
+        double* saux = reinterpret_cast<double*>(dsm) + ((size_t)a.elems * t.T * 2 + 2 * t.T + (a.nmasks + 3) / 4 * 2);   // 16-byte aligned
+        for (int k = threadIdx.x; k < a.aux_smem; k += THREADS) saux[k] = __ldg(a0.aux + k);
+        a.aux = saux;   // published by the barrier of the first op-chunk refill
+    }
     const uint32_t tmask = t.T == 32 ? 0xffffffffu : ((1u << t.T) - 1u);
     for (int64_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
         const int64_t t0 = tile << a.logT, t_loc = t0 + t.lane;
@@ -293,7 +299,7 @@ __global__ void __launch_bounds__(QSB_DEXEC_THREADS, MINB) k_dense_exec(DExecArg
                 const int nchunk = min(QSB_DEXEC_CHUNK, a.nops - i);
                 const uint4* src = reinterpret_cast<const uint4*>(a.ops + i);
                 uint4* dst = reinterpret_cast<uint4*>(sops);
-                for (int k = threadIdx.x; k < nchunk * (int)(sizeof(DExecOp) / 16); k += blockDim.x) dst[k] = __ldg(src + k);
+                for (int k = threadIdx.x; k < nchunk * (int)(sizeof(DExecOp) / 16); k += THREADS) dst[k] = __ldg(src + k);
                 __syncthreads();
             }
             const DExecOp& op = sops[i % QSB_DEXEC_CHUNK];
@@ -302,7 +308,7 @@ __global__ void __launch_bounds__(QSB_DEXEC_THREADS, MINB) k_dense_exec(DExecArg
             case DOP_CONST: {
                 const int L = 1 << (2 * op.n);
                 const double2* src = reinterpret_cast<const double2*>(a.aux + op.aux);
-                for (int e = t.grp; e < L; e += t.G) t.at(op.s[0], e) = __ldg(src + e);
+                for (int e = t.grp; e < L; e += t.G) t.at(op.s[0], e) = src[e];
                 if (threadIdx.x == 0) t.masks[op.al[0]] = validw;
                 break;
             }
@@ -340,7 +346,7 @@ __global__ void __launch_bounds__(QSB_DEXEC_THREADS, MINB) k_dense_exec(DExecArg
                 break;
             case TOP_MASK_RANDOM:
                 if (t.grp == op.grp) {
-                    const double p = __ldg(a.aux + op.aux);
+                    const double p = a.aux[op.aux];
                     const bool b = qsb_draw(a.seed, traj, (uint64_t)op.draw + a.draw_base) < p;
                     const uint32_t w = (__ballot_sync(t.gmask, b) >> t.gshift) & tmask;
                     if (t.lane == 0) t.masks[op.m[0]] = w & validw;
@@ -361,7 +367,7 @@ struct qsb_dprogram {
     qsb_ctx* ctx;
     DExecOp* d_ops; DExecOp* h_ops; int nops;
     double* d_aux; int naux;
-    int elems, nmasks, logT, blocks_per_sm, smem_bytes, barriers;
+    int elems, nmasks, logT, blocks_per_sm, smem_bytes, barriers, threads, variant, aux_smem, regs;
     uint64_t per_traj_rows, nstats;
 };
 
@@ -399,35 +405,10 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     qsb_dprogram* P = new qsb_dprogram();
     memset(P, 0, sizeof(*P));
     P->ctx = ctx; P->elems = elems > 0 ? elems : 1; P->nmasks = nmasks > 0 ? nmasks : 1;
-    // launch shape: T lanes per tile (32, 16 or 8); prefer the shape that keeps the most trajectories, then the most warps, resident per SM
-    int dev_smem = 0, sm_smem = 0;
-    cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
-    cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
-    cudaFuncAttributes fa, fa1;
-    if (cudaFuncGetAttributes(&fa1, k_dense_exec<1>) != cudaSuccess || cudaFuncGetAttributes(&fa, k_dense_exec<2>) != cudaSuccess) { cudaGetLastError(); delete P; QSB_FAIL(QSB_ERR_CUDA, "k_dense_exec is not loadable on this device"); }
-    const char* force = getenv("QSB_DEXEC_T");
-    long best = -1;
-    for (int logT = 5; logT >= 3; --logT) {
-        const int T = 1 << logT;
-        if (force && atoi(force) != T) continue;
-        size_t smem = (size_t)P->elems * T * sizeof(double2) + 2 * T * sizeof(double) + (size_t)P->nmasks * sizeof(uint32_t);
-        smem = (smem + 15) / 16 * 16;
-        if (smem + fa.sharedSizeBytes > (size_t)dev_smem) continue;
-        int bps = (int)((size_t)sm_smem / (smem + fa.sharedSizeBytes + 1024));
-        int by_regs = 65536 / (fa.numRegs * QSB_DEXEC_THREADS > 0 ? fa.numRegs * QSB_DEXEC_THREADS : 1);
-        if (bps > by_regs) bps = by_regs;
-        if (bps > 8) bps = 8;
-        if (bps < 1) bps = 1;
-        long rank = (long)T * bps * 100 + bps;
-        if (rank > best) { best = rank; P->logT = logT; P->blocks_per_sm = bps; P->smem_bytes = (int)smem; }
-    }
-    if (best < 0) { delete P; QSB_FAIL(QSB_ERR_UNSUPPORTED, "the recorded dense program keeps %d matrix elements per trajectory alive: it does not fit in shared memory even 8 trajectories at a time", elems); }
-    const int G = QSB_DEXEC_THREADS >> P->logT;
     // ops, barrier flags, group assignment
     std::vector<DExecOp> xops;
     std::vector<double> aux = R->daux;
     Access acc;
-    int rr = 0;
     for (size_t i = 0; i < R->ops.size(); ++i) {
         const TabOp& o = R->ops[i];
         if (o.type == TOP_NOP) continue;
@@ -446,7 +427,6 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
             for (int e = 0; e < MM; ++e) if (aux[o.obs + 2 * e] != 0.0 || aux[o.obs + 2 * e + 1] != 0.0) x.u[0] |= 1u << e;
         } else if (o.type == TOP_MASK_FILL || o.type == TOP_MASK_LOGIC) x.mode = (uint8_t)o.iv[0];
         else if (o.type == TOP_MASK_RANDOM) { if (aux.size() & 1) aux.push_back(0.0); x.aux = (int32_t)aux.size(); aux.push_back(o.f[0]); }
-        if (o.type == DOP_MEASURE || o.type == DOP_EXPECT || o.type == TOP_MASK_RANDOM) x.grp = (uint16_t)(rr++ % G);
         if (o.draw > 0xffffffffull || P->nmasks > 32767) { delete P; QSB_FAIL(QSB_ERR_UNSUPPORTED, "program too large for the dense executor's op encoding"); }
         // barrier before this op when it touches storage an op since the last barrier wrote (or writes what one read)
         Access A = access_of(o);
@@ -459,6 +439,42 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
         xops.push_back(x);
     }
     P->nops = (int)xops.size(); P->naux = (int)aux.size(); P->nstats = R->stats_ptrs.size();
+    // launch shape: T lanes per tile (32, 16 or 8) x block variant.  The executor is latency bound (a tile walks its op list
+    // serially), so throughput follows the number of trajectories resident per SM: rank by resident trajectories, then by tile width.  QSB_DEXEC_T / QSB_DEXEC_THREADS pin the shape (tuning aid).
+    int dev_smem = 0, sm_smem = 0;
+    cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
+    cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
+    cudaFuncAttributes fa[3];
+    const int vthreads[3] = {256, 256, 128};
+    if (cudaFuncGetAttributes(&fa[0], k_dense_exec<256, 1>) != cudaSuccess || cudaFuncGetAttributes(&fa[1], k_dense_exec<256, 2>) != cudaSuccess ||
+        cudaFuncGetAttributes(&fa[2], k_dense_exec<128, 4>) != cudaSuccess) { cudaGetLastError(); delete P; QSB_FAIL(QSB_ERR_CUDA, "k_dense_exec is not loadable on this device"); }
+    const char *force_t = getenv("QSB_DEXEC_T"), *force_v = getenv("QSB_DEXEC_VARIANT");
+    const int aux_smem = P->naux * 8 <= 16384 ? (P->naux + 1) / 2 * 2 : 0;
+    long best = -1;
+    for (int v = 0; v < 3; ++v) for (int logT = 5; logT >= 3; --logT) {
+        const int T = 1 << logT;
+        if ((force_t && atoi(force_t) != T) || (force_v && atoi(force_v) != v)) continue;
+        size_t smem = (size_t)P->elems * T * sizeof(double2) + 2 * T * sizeof(double) + (size_t)(P->nmasks + 3) / 4 * 16 + (size_t)aux_smem * 8;
+        smem = (smem + 15) / 16 * 16;
+        if (smem + fa[v].sharedSizeBytes > (size_t)dev_smem) continue;
+        int bps = (int)((size_t)sm_smem / (smem + fa[v].sharedSizeBytes + 1024));
+        const int by_regs = 65536 / (fa[v].numRegs * vthreads[v]);
+        if (bps > by_regs) bps = by_regs;
+        if (bps > 16) bps = 16;
+        if (bps < 1) continue;
+        if (v == 0 && bps > 1) bps = 1;   // the 255-register variant is for arenas that fill an SM
+        // measured on B200 (tools/sweep_dexec.sh, firstgenrepeater dm): at equal resident trajectories the widest tile wins
+        // (32 x 1 block: 349 ms, 16 x 2: 398 ms, 8 x 4: 456 ms per 10^6 trajectories)
+        const long rank = (long)T * bps * 10000 + (long)T * 10 + (2 - v);
+        if (rank > best) { best = rank; P->logT = logT; P->blocks_per_sm = bps; P->smem_bytes = (int)smem; P->variant = v; P->threads = vthreads[v]; P->regs = fa[v].numRegs; }
+    }
+    if (best < 0) { delete P; QSB_FAIL(QSB_ERR_UNSUPPORTED, "the recorded dense program keeps %d matrix elements per trajectory alive: it does not fit in shared memory even 8 trajectories at a time", elems); }
+    P->aux_smem = aux_smem;
+    {   // the single-group parts of ops (measurement decision, observables, random masks) rotate over the groups
+        const int G = P->threads >> P->logT;
+        int rr = 0;
+        for (auto& x : xops) if (x.type == DOP_MEASURE || x.type == DOP_EXPECT || x.type == TOP_MASK_RANDOM) x.grp = (uint16_t)(rr++ % G);
+    }
     int rc = QSB_OK;
     if (!xops.empty()) {
         if (cudaMallocHost((void**)&P->h_ops, xops.size() * sizeof(DExecOp)) != cudaSuccess) { cudaGetLastError(); qsb_set_error("pinned allocation of the op list failed"); rc = QSB_ERR_OOM; }
@@ -469,11 +485,12 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     if (rc == QSB_OK && !xops.empty() && cudaMemcpyAsync(P->d_ops, P->h_ops, xops.size() * sizeof(DExecOp), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) rc = QSB_ERR_CUDA;
     if (rc == QSB_OK && !aux.empty() && cudaMemcpyAsync(P->d_aux, aux.data(), aux.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) rc = QSB_ERR_CUDA;
     if (rc == QSB_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = QSB_ERR_CUDA;   // `aux` dies below
-    if (rc == QSB_OK && (cudaFuncSetAttribute(k_dense_exec<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa1.sharedSizeBytes) != cudaSuccess ||
-                         cudaFuncSetAttribute(k_dense_exec<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa.sharedSizeBytes) != cudaSuccess)) rc = QSB_ERR_CUDA;
+    if (rc == QSB_OK && (cudaFuncSetAttribute(k_dense_exec<256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa[0].sharedSizeBytes) != cudaSuccess ||
+                         cudaFuncSetAttribute(k_dense_exec<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa[1].sharedSizeBytes) != cudaSuccess ||
+                         cudaFuncSetAttribute(k_dense_exec<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa[2].sharedSizeBytes) != cudaSuccess)) rc = QSB_ERR_CUDA;
     if (rc != QSB_OK) { if (rc == QSB_ERR_CUDA) { qsb_set_error("dense program upload failed: %s", cudaGetErrorString(cudaGetLastError())); } qsb_dexec_free(P); return rc; }
-    if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] dense program: %d ops, %d barriers, %d elements, %d mask words, T=%d, %d block(s)/SM, %d B smem, %d regs\n",
-                                         P->nops, P->barriers, P->elems, P->nmasks, 1 << P->logT, P->blocks_per_sm, P->smem_bytes, fa.numRegs);
+    if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] dense program: %d ops, %d barriers, %d elements, %d mask words, %d aux doubles (%s), T=%d, %d threads, %d block(s)/SM, %d B smem, %d regs\n",
+                                         P->nops, P->barriers, P->elems, P->nmasks, P->naux, P->aux_smem ? "smem" : "global", 1 << P->logT, P->threads, P->blocks_per_sm, P->smem_bytes, P->regs);
     *out = P;
     return QSB_OK;
 }
@@ -481,14 +498,15 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
 int qsb_dexec_run(qsb_dprogram* P, uint64_t traj_shift, uint64_t draw_base) {
     qsb_ctx* ctx = P->ctx;
     DExecArgs a;
-    a.ops = P->d_ops; a.nops = P->nops; a.aux = P->d_aux; a.elems = P->elems; a.nmasks = P->nmasks; a.logT = P->logT;
+    a.ops = P->d_ops; a.nops = P->nops; a.aux = P->d_aux; a.elems = P->elems; a.nmasks = P->nmasks; a.logT = P->logT; a.aux_smem = P->aux_smem;
     a.valid = ctx->valid; a.ntiles = ctx->npad >> P->logT;
     a.seed = ctx->seed; a.traj0 = (uint64_t)ctx->traj_offset + traj_shift; a.draw_base = draw_base; a.flags = ctx->dev_flags;
     int64_t blocks = (int64_t)ctx->sm_count * P->blocks_per_sm;
     if (blocks > a.ntiles) blocks = a.ntiles;
     QSB_PRE(ctx, "k_dense_exec");
-    if (P->blocks_per_sm >= 2) k_dense_exec<2><<<(unsigned)blocks, QSB_DEXEC_THREADS, P->smem_bytes, ctx->stream>>>(a);
-    else k_dense_exec<1><<<(unsigned)blocks, QSB_DEXEC_THREADS, P->smem_bytes, ctx->stream>>>(a);
+    if (P->variant == 0) k_dense_exec<256, 1><<<(unsigned)blocks, 256, P->smem_bytes, ctx->stream>>>(a);
+    else if (P->variant == 1) k_dense_exec<256, 2><<<(unsigned)blocks, 256, P->smem_bytes, ctx->stream>>>(a);
+    else k_dense_exec<128, 4><<<(unsigned)blocks, 128, P->smem_bytes, ctx->stream>>>(a);
     QSB_LAUNCH_CHECK(ctx);
     // compulsory HBM traffic of the fused launch: op list + constants once, statistics and per-trajectory rows written once
     qsb_account(ctx, "k_dense_exec", (uint64_t)P->nops * sizeof(DExecOp) + (uint64_t)P->naux * 8 + P->nstats * 32 + P->per_traj_rows * (uint64_t)ctx->npad * 16);
@@ -503,7 +521,7 @@ int qsb_dexec_upload(qsb_dprogram* P, int64_t* bytes) {
 }
 
 void qsb_dexec_info(const qsb_dprogram* P, int64_t info[8]) {
-    info[0] = P->nops; info[1] = P->elems; info[3] = QSB_DEXEC_THREADS; info[4] = P->smem_bytes; info[5] = 0;
+    info[0] = P->nops; info[1] = P->elems; info[3] = P->threads; info[4] = P->smem_bytes; info[5] = 0;
 }
 int qsb_dexec_tile(const qsb_dprogram* P) { return 1 << P->logT; }
 int qsb_dexec_barriers(const qsb_dprogram* P) { return P->barriers; }

@@ -40,6 +40,7 @@ struct DExecArgs {
     const DExecOp* ops; int nops;
     const double* aux;
     int elems, nmasks, logT;         // arena elements per trajectory, mask words, log2(T)
+    int aux_smem;                    // > 0: the aux table (this many doubles) is copied into shared memory at kernel start
     const uint32_t* valid;
     int64_t ntiles;
     uint64_t seed, traj0, draw_base;

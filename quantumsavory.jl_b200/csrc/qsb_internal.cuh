@@ -62,6 +62,7 @@ struct qsb_state {
     size_t bytes;
     uint32_t* alive;  // [nwords]
     int vbase, valive; // record mode: plane indices inside the program arena (data == alive == nullptr)
+    int vcap;          // record mode, dense: elements the state's arena block was allocated with
     int gen;           // recording generation the virtual planes belong to
 };
 
