@@ -259,10 +259,12 @@ class GpuRun:
         self.program.run(traj_shift=self.batch * self.ntraj * self.world)
         return self.program_log
 
-    def finish_step(self):
-        """The step's result crosses GPUs (one all-reduce) and comes back to the host (D2H)."""
+    def finish_step(self, reduce=True):
+        """The step's result crosses GPUs (one all-reduce) and comes back to the host (D2H).
+        reduce=False: rank-local read-back (the profiled extra step runs on rank 0 only -- no collective there)."""
         with self.torch.cuda.stream(self.stream):
-            self.stats.allreduce()
+            if reduce:
+                self.stats.allreduce()
             host = self.stats.t[: max(self.nobs, 1)].cpu()
         return host.numpy()
 
@@ -325,7 +327,7 @@ def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, pr
         out["program"] = dict(g.program.info(), record_ms=g.record_ms)
     if profile and rank == 0:
         ctx.profile(True)
-        do_step(); g.finish_step()
+        do_step(); g.finish_step(reduce=False)
         rows = ctx.profile_report()
         ctx.profile(False)
         rows = [r for r in rows if r["launches"]]
@@ -366,7 +368,20 @@ def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, pr
     return out
 
 
+def _emit(line: dict):
+    """The ONE JSON line goes to the process's real stdout; everything else printed while the bench runs (NCCL's
+    version banner, library chatter) was redirected to stderr so that stdout stays machine-readable."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -402,7 +417,7 @@ def main():
             vals.append(r["ntraj"] / r["wall"])
         v = float(np.median(vals))
         sample = f"{per_core} trajectories per core x {r['cores']} cores per step, {args.steps} steps (median)"
-        print(json.dumps({"impl": "reference", "metric": "trajectories/sec", "value": v, "unit": "trajectories/s", "n_gpus": args.gpus,
+        _emit(({"impl": "reference", "metric": "trajectories/sec", "value": v, "unit": "trajectories/s", "n_gpus": args.gpus,
                           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * r["wall"], "higher_is_better": True,
                           "scaling": "weak", "vs_baseline": None, "dtype": "u32 bit-sliced tableau" if w["formalism"] == "clifford" else "f64 complex",
                           "data": "synthetic", "config": config,
@@ -454,7 +469,7 @@ def main():
                 "state_ops_per_sec": main_res["ops_per_step"] * world / (main_res["dev_ms_per_step"] * 1e-3),
                 "roofline": main_res.get("roofline"), "kernels": main_res.get("kernels"), "cpu_baseline": cpu,
                 "workload_log": main_res["log"], "extra": extra}
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
