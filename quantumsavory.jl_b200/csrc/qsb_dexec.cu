@@ -85,6 +85,53 @@ __device__ __forceinline__ void d_apply(const DTile& t, const DExecOp& op, const
     }
 }
 
+// Generalised-permutation gates (one non-zero per row: Paulis, CNOT, CPHASE, ZCY, ...): out[r][c] = w_r conj(w_c) x[p(r)][p(c)].
+// op.u[0] packs p (K bits per row), op.u[1] marks the (r,c) whose coefficient differs from 1, aux holds the coefficients.
+// No M^3 products and no bit tests: 2 M^2 shared-memory accesses per block and at most M^2 complex multiplies.
+template <int K>
+__device__ __forceinline__ void d_apply_perm(const DTile& t, const DExecOp& op, const double* __restrict__ aux) {
+    constexpr int M = 1 << K;
+    if (op.m[0] >= 0 && !((t.masks[op.m[0]] >> t.lane) & 1u)) return;
+    const int n = op.n, base0 = op.s[0];
+    int pos[K], sorted[2 * K];
+#pragma unroll
+    for (int i = 0; i < K; ++i) pos[i] = op.q[i];
+    if constexpr (K == 1) { sorted[0] = pos[0]; sorted[1] = pos[0] + n; }
+    else {
+        const int lo = min(pos[0], pos[1]), hi = max(pos[0], pos[1]);
+        sorted[0] = lo; sorted[1] = hi; sorted[2] = lo + n; sorted[3] = hi + n;
+    }
+    int dst[M], src[M];   // row-bit patterns of the block's rows, and of the rows they are fetched from
+#pragma unroll
+    for (int r = 0; r < M; ++r) {
+        int d = 0, sidx = (int)(op.u[0] >> (K * r)) & (M - 1), sbits = 0;
+#pragma unroll
+        for (int j = 0; j < K; ++j) { d |= ((r >> j) & 1) << pos[j]; sbits |= ((sidx >> j) & 1) << pos[j]; }
+        dst[r] = d; src[r] = sbits;
+    }
+    const uint32_t cm = op.u[1];
+    const double2* C = reinterpret_cast<const double2*>(aux + op.aux);
+    const int groups = 1 << (2 * n - 2 * K);
+    for (int g = t.grp; g < groups; g += t.G) {
+        int b = g;
+#pragma unroll
+        for (int i = 0; i < 2 * K; ++i) b = ins0(b, sorted[i]);
+        double2 v[M][M];
+#pragma unroll
+        for (int r = 0; r < M; ++r)
+#pragma unroll
+            for (int c = 0; c < M; ++c) v[r][c] = t.at(base0, b | src[r] | (src[c] << n));
+#pragma unroll
+        for (int r = 0; r < M; ++r)
+#pragma unroll
+            for (int c = 0; c < M; ++c) {
+                double2 o = v[r][c];
+                if ((cm >> (r + c * M)) & 1u) o = cmul(C[r + c * M], o);
+                t.at(base0, b | dst[r] | (dst[c] << n)) = o;
+            }
+    }
+}
+
 // closed-form single-qubit channel on the 2x2 blocks of qubit q (coefficients a, b, c, dd, f; see qsb_dense.cu)
 __device__ __forceinline__ void d_channel(const DTile& t, const DExecOp& op, const double* __restrict__ aux) {
     const double* p = aux + op.aux;
@@ -269,11 +316,14 @@ __device__ __forceinline__ void d_expect(const DTile& t, const DExecOp& op, cons
 }
 
 // THREADS x MINB: block size and the blocks per SM the register allocation must allow -- 256x1 (up to 255 registers) for
-// programs whose arena fills an SM, 256x2 and 128x4 (128 registers) for smaller arenas where several tiles share an SM.
+// programs whose arena fills an SM, 256x2 and 128x4 (128 registers) for smaller arenas where several tiles share an SM, and
+// 32xN: ONE WARP per tile of 8 or 4 trajectories (4 or 8 groups inside the warp) -- no idle warps decoding ops they have no
+// items for, block barriers degenerate to warp barriers, and 5-10 independent tiles per SM hide each other's latency.
 template <int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB) k_dense_exec(DExecArgs a0) {
     extern __shared__ double2 dsm[];
-    __shared__ DExecOp sops[QSB_DEXEC_CHUNK];
+    constexpr int CHUNK = QSB_DEXEC_CHUNK_OF(THREADS);
+    __shared__ DExecOp sops[CHUNK];
     DExecArgs a = a0;
     DTile t;
     t.logT = a.logT; t.T = 1 << a.logT; t.G = THREADS >> a.logT;
@@ -294,15 +344,15 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dense_exec(DExecArgs a0) {
         const uint64_t traj = a.traj0 + (uint64_t)t_loc;
         const uint32_t validw = (a.valid[t0 >> 5] >> (t0 & 31)) & tmask;
         for (int i = 0; i < a.nops; ++i) {
-            if ((i % QSB_DEXEC_CHUNK) == 0) {   // refill (also the barrier between tiles)
+            if ((i % CHUNK) == 0) {   // refill (also the barrier between tiles)
                 __syncthreads();
-                const int nchunk = min(QSB_DEXEC_CHUNK, a.nops - i);
+                const int nchunk = min(CHUNK, a.nops - i);
                 const uint4* src = reinterpret_cast<const uint4*>(a.ops + i);
                 uint4* dst = reinterpret_cast<uint4*>(sops);
                 for (int k = threadIdx.x; k < nchunk * (int)(sizeof(DExecOp) / 16); k += THREADS) dst[k] = __ldg(src + k);
                 __syncthreads();
             }
-            const DExecOp& op = sops[i % QSB_DEXEC_CHUNK];
+            const DExecOp& op = sops[i % CHUNK];
             if (op.flags & 1) __syncthreads();
             switch (op.type) {
             case DOP_CONST: {
@@ -319,7 +369,10 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dense_exec(DExecArgs a0) {
                 break;
             }
             case DOP_TENSOR: d_tensor(t, op); break;
-            case DOP_APPLY: if (op.k == 1) d_apply<1>(t, op, a.aux); else d_apply<2>(t, op, a.aux); break;
+            case DOP_APPLY:
+                if (op.mode == 1) { if (op.k == 1) d_apply_perm<1>(t, op, a.aux); else d_apply_perm<2>(t, op, a.aux); }
+                else if (op.k == 1) d_apply<1>(t, op, a.aux); else d_apply<2>(t, op, a.aux);
+                break;
             case DOP_CHANNEL: d_channel(t, op, a.aux); break;
             case DOP_MEASURE:
                 if (t.grp == op.grp) d_measure_decide(t, op, a, traj);
@@ -408,7 +461,8 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     // ops, barrier flags, group assignment
     std::vector<DExecOp> xops;
     std::vector<double> aux = R->daux;
-    Access acc;
+    std::vector<int> src;   // xops[j] came from R->ops[src[j]]
+    std::map<int, int> coef_at;
     for (size_t i = 0; i < R->ops.size(); ++i) {
         const TabOp& o = R->ops[i];
         if (o.type == TOP_NOP) continue;
@@ -423,19 +477,39 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
             x.fpow = o.f[0] > 0.5 ? 0u : o.f[0] < -0.5 ? 2u : o.f[1] > 0.5 ? 1u : 3u;
             if (o.per_traj) P->per_traj_rows++;
         } else if (o.type == DOP_APPLY) {
-            const int MM = 1 << (2 * o.k);
+            const int M = 1 << o.k, MM = M * M;
             for (int e = 0; e < MM; ++e) if (aux[o.obs + 2 * e] != 0.0 || aux[o.obs + 2 * e + 1] != 0.0) x.u[0] |= 1u << e;
+            // one non-zero per row and per column: a generalised permutation, applied by moving elements (d_apply_perm)
+            int p[4] = {0, 0, 0, 0}, colseen = 0; bool gperm = true;
+            for (int r = 0; r < M && gperm; ++r) {
+                int cnt = 0;
+                for (int m = 0; m < M; ++m) if ((x.u[0] >> (r + m * M)) & 1u) { p[r] = m; ++cnt; }
+                if (cnt != 1 || ((colseen >> p[r]) & 1)) gperm = false;
+                colseen |= 1 << p[r];
+            }
+            if (gperm) {
+                std::vector<double> coef(2 * MM);
+                uint32_t perm = 0, cmask = 0;
+                for (int r = 0; r < M; ++r) perm |= (uint32_t)p[r] << (o.k * r);
+                for (int c = 0; c < M; ++c) for (int r = 0; r < M; ++r) {   // coefficient w_r conj(w_c), w_r = U[r][p(r)]
+                    const double ar = aux[o.obs + 2 * (r + p[r] * M)], ai = aux[o.obs + 2 * (r + p[r] * M) + 1];
+                    const double br = aux[o.obs + 2 * (c + p[c] * M)], bi = aux[o.obs + 2 * (c + p[c] * M) + 1];
+                    const double re = ar * br + ai * bi, im = ai * br - ar * bi;
+                    coef[2 * (r + c * M)] = re; coef[2 * (r + c * M) + 1] = im;
+                    if (re != 1.0 || im != 0.0) cmask |= 1u << (r + c * M);
+                }
+                auto hit = coef_at.find(o.obs);   // the same gate matrix (deduplicated payload) shares one coefficient table
+                if (hit == coef_at.end()) {
+                    if (aux.size() & 1) aux.push_back(0.0);
+                    hit = coef_at.insert({o.obs, (int)aux.size()}).first;
+                    aux.insert(aux.end(), coef.begin(), coef.end());
+                }
+                x.aux = hit->second; x.mode = 1; x.u[0] = perm; x.u[1] = cmask;
+            }
         } else if (o.type == TOP_MASK_FILL || o.type == TOP_MASK_LOGIC) x.mode = (uint8_t)o.iv[0];
         else if (o.type == TOP_MASK_RANDOM) { if (aux.size() & 1) aux.push_back(0.0); x.aux = (int32_t)aux.size(); aux.push_back(o.f[0]); }
         if (o.draw > 0xffffffffull || P->nmasks > 32767) { delete P; QSB_FAIL(QSB_ERR_UNSUPPORTED, "program too large for the dense executor's op encoding"); }
-        // barrier before this op when it touches storage an op since the last barrier wrote (or writes what one read)
-        Access A = access_of(o);
-        const bool refill = (xops.size() % QSB_DEXEC_CHUNK) == 0;   // the chunk refill is a barrier already
-        bool need = overlap(A.w, acc.r) || overlap(A.w, acc.w) || overlap(A.r, acc.w);
-        if (refill) { acc = Access(); need = false; }
-        if (need) { x.flags |= 1; P->barriers++; acc = Access(); }
-        if (o.type == DOP_MEASURE || o.type == DOP_PTRACE) { acc = Access(); acc.w = {Span{o.s[0], o.s[0] + (1 << (2 * o.n))}}; if (o.type == DOP_MEASURE) acc.w.push_back(Span{MASK0 + o.m[0], MASK0 + o.m[0] + 1}); }
-        else { acc.r.insert(acc.r.end(), A.r.begin(), A.r.end()); acc.w.insert(acc.w.end(), A.w.begin(), A.w.end()); }
+        src.push_back((int)i);
         xops.push_back(x);
     }
     P->nops = (int)xops.size(); P->naux = (int)aux.size(); P->nstats = R->stats_ptrs.size();
@@ -444,15 +518,19 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     int dev_smem = 0, sm_smem = 0;
     cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
     cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
-    cudaFuncAttributes fa[3];
-    const int vthreads[3] = {256, 256, 128};
-    if (cudaFuncGetAttributes(&fa[0], k_dense_exec<256, 1>) != cudaSuccess || cudaFuncGetAttributes(&fa[1], k_dense_exec<256, 2>) != cudaSuccess ||
-        cudaFuncGetAttributes(&fa[2], k_dense_exec<128, 4>) != cudaSuccess) { cudaGetLastError(); delete P; QSB_FAIL(QSB_ERR_CUDA, "k_dense_exec is not loadable on this device"); }
+    const int NV = 5;
+    cudaFuncAttributes fa[NV];
+    const int vthreads[NV] = {256, 256, 128, 32, 32};
+    const void* vfn[NV] = {(const void*)k_dense_exec<256, 1>, (const void*)k_dense_exec<256, 2>, (const void*)k_dense_exec<128, 4>,
+                           (const void*)k_dense_exec<32, 8>, (const void*)k_dense_exec<32, 16>};
+    for (int v = 0; v < NV; ++v)
+        if (cudaFuncGetAttributes(&fa[v], vfn[v]) != cudaSuccess) { cudaGetLastError(); delete P; QSB_FAIL(QSB_ERR_CUDA, "k_dense_exec is not loadable on this device"); }
     const char *force_t = getenv("QSB_DEXEC_T"), *force_v = getenv("QSB_DEXEC_VARIANT");
     const int aux_smem = P->naux * 8 <= 16384 ? (P->naux + 1) / 2 * 2 : 0;
     long best = -1;
-    for (int v = 0; v < 3; ++v) for (int logT = 5; logT >= 3; --logT) {
+    for (int v = 0; v < NV; ++v) for (int logT = 5; logT >= 2; --logT) {
         const int T = 1 << logT;
+        if (T > vthreads[v] || (vthreads[v] == 32 && T > 8)) continue;
         if ((force_t && atoi(force_t) != T) || (force_v && atoi(force_v) != v)) continue;
         size_t smem = (size_t)P->elems * T * sizeof(double2) + 2 * T * sizeof(double) + (size_t)(P->nmasks + 3) / 4 * 16 + (size_t)aux_smem * 8;
         smem = (smem + 15) / 16 * 16;
@@ -460,12 +538,12 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
         int bps = (int)((size_t)sm_smem / (smem + fa[v].sharedSizeBytes + 1024));
         const int by_regs = 65536 / (fa[v].numRegs * vthreads[v]);
         if (bps > by_regs) bps = by_regs;
-        if (bps > 16) bps = 16;
+        if (bps > 24) bps = 24;
         if (bps < 1) continue;
         if (v == 0 && bps > 1) bps = 1;   // the 255-register variant is for arenas that fill an SM
         // measured on B200 (tools/sweep_dexec.sh, firstgenrepeater dm): at equal resident trajectories the widest tile wins
         // (32 x 1 block: 349 ms, 16 x 2: 398 ms, 8 x 4: 456 ms per 10^6 trajectories)
-        const long rank = (long)T * bps * 10000 + (long)T * 10 + (2 - v);
+        const long rank = (long)T * bps * 10000 + (long)T * 10 + (NV - v);
         if (rank > best) { best = rank; P->logT = logT; P->blocks_per_sm = bps; P->smem_bytes = (int)smem; P->variant = v; P->threads = vthreads[v]; P->regs = fa[v].numRegs; }
     }
     if (best < 0) { delete P; QSB_FAIL(QSB_ERR_UNSUPPORTED, "the recorded dense program keeps %d matrix elements per trajectory alive: it does not fit in shared memory even 8 trajectories at a time", elems); }
@@ -474,6 +552,19 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
         const int G = P->threads >> P->logT;
         int rr = 0;
         for (auto& x : xops) if (x.type == DOP_MEASURE || x.type == DOP_EXPECT || x.type == TOP_MASK_RANDOM) x.grp = (uint16_t)(rr++ % G);
+        // barrier before an op when it touches storage an op since the last barrier wrote (or writes what one read); the
+        // op-chunk refill of the chosen block variant is a barrier already
+        const int chunk = QSB_DEXEC_CHUNK_OF(P->threads);
+        Access acc;
+        for (size_t j = 0; j < xops.size(); ++j) {
+            const TabOp& o = R->ops[src[j]];
+            Access A = access_of(o);
+            bool need = overlap(A.w, acc.r) || overlap(A.w, acc.w) || overlap(A.r, acc.w);
+            if ((j % chunk) == 0) { acc = Access(); need = false; }
+            if (need) { xops[j].flags |= 1; P->barriers++; acc = Access(); }
+            if (o.type == DOP_MEASURE || o.type == DOP_PTRACE) { acc = Access(); acc.w = {Span{o.s[0], o.s[0] + (1 << (2 * o.n))}}; if (o.type == DOP_MEASURE) acc.w.push_back(Span{MASK0 + o.m[0], MASK0 + o.m[0] + 1}); }
+            else { acc.r.insert(acc.r.end(), A.r.begin(), A.r.end()); acc.w.insert(acc.w.end(), A.w.begin(), A.w.end()); }
+        }
     }
     int rc = QSB_OK;
     if (!xops.empty()) {
@@ -485,9 +576,8 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     if (rc == QSB_OK && !xops.empty() && cudaMemcpyAsync(P->d_ops, P->h_ops, xops.size() * sizeof(DExecOp), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) rc = QSB_ERR_CUDA;
     if (rc == QSB_OK && !aux.empty() && cudaMemcpyAsync(P->d_aux, aux.data(), aux.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) rc = QSB_ERR_CUDA;
     if (rc == QSB_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = QSB_ERR_CUDA;   // `aux` dies below
-    if (rc == QSB_OK && (cudaFuncSetAttribute(k_dense_exec<256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa[0].sharedSizeBytes) != cudaSuccess ||
-                         cudaFuncSetAttribute(k_dense_exec<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa[1].sharedSizeBytes) != cudaSuccess ||
-                         cudaFuncSetAttribute(k_dense_exec<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa[2].sharedSizeBytes) != cudaSuccess)) rc = QSB_ERR_CUDA;
+    for (int v = 0; v < NV && rc == QSB_OK; ++v)
+        if (cudaFuncSetAttribute(vfn[v], cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa[v].sharedSizeBytes) != cudaSuccess) rc = QSB_ERR_CUDA;
     if (rc != QSB_OK) { if (rc == QSB_ERR_CUDA) { qsb_set_error("dense program upload failed: %s", cudaGetErrorString(cudaGetLastError())); } qsb_dexec_free(P); return rc; }
     if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] dense program: %d ops, %d barriers, %d elements, %d mask words, %d aux doubles (%s), T=%d, %d threads, %d block(s)/SM, %d B smem, %d regs\n",
                                          P->nops, P->barriers, P->elems, P->nmasks, P->naux, P->aux_smem ? "smem" : "global", 1 << P->logT, P->threads, P->blocks_per_sm, P->smem_bytes, P->regs);
@@ -506,7 +596,9 @@ int qsb_dexec_run(qsb_dprogram* P, uint64_t traj_shift, uint64_t draw_base) {
     QSB_PRE(ctx, "k_dense_exec");
     if (P->variant == 0) k_dense_exec<256, 1><<<(unsigned)blocks, 256, P->smem_bytes, ctx->stream>>>(a);
     else if (P->variant == 1) k_dense_exec<256, 2><<<(unsigned)blocks, 256, P->smem_bytes, ctx->stream>>>(a);
-    else k_dense_exec<128, 4><<<(unsigned)blocks, 128, P->smem_bytes, ctx->stream>>>(a);
+    else if (P->variant == 2) k_dense_exec<128, 4><<<(unsigned)blocks, 128, P->smem_bytes, ctx->stream>>>(a);
+    else if (P->variant == 3) k_dense_exec<32, 8><<<(unsigned)blocks, 32, P->smem_bytes, ctx->stream>>>(a);
+    else k_dense_exec<32, 16><<<(unsigned)blocks, 32, P->smem_bytes, ctx->stream>>>(a);
     QSB_LAUNCH_CHECK(ctx);
     // compulsory HBM traffic of the fused launch: op list + constants once, statistics and per-trajectory rows written once
     qsb_account(ctx, "k_dense_exec", (uint64_t)P->nops * sizeof(DExecOp) + (uint64_t)P->naux * 8 + P->nstats * 32 + P->per_traj_rows * (uint64_t)ctx->npad * 16);

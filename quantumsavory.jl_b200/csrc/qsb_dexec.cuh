@@ -33,7 +33,7 @@ struct DExecOp {              // 80 bytes (five 16-byte words: staged through sh
     uint64_t reserved1;
 };
 static_assert(sizeof(DExecOp) == 80, "DExecOp layout");
-#define QSB_DEXEC_CHUNK 32           // ops staged per shared-memory refill
+#define QSB_DEXEC_CHUNK_OF(threads) ((threads) >= 128 ? 32 : 8)   // ops staged per shared-memory refill (80 B each, per block)
 #define QSB_DEXEC_THREADS 256
 
 struct DExecArgs {

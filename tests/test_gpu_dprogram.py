@@ -70,7 +70,7 @@ def test_dense_program_matches_per_op_path(ntraj, bgname):
 
     def close(a, b, what):
         a, b = a.cpu().numpy(), b.cpu().numpy()
-        scale = max(np.abs(a).max(), 1e-300)
+        scale = max(np.abs(a).max(), 1.0)      # observables and statistics-per-trajectory are O(1): 1e-12 absolute below that
         assert np.abs(a - b).max() <= RTOL * scale, (what, np.abs(a - b).max(), scale)
 
     ctx = BatchContext(ntraj, seed=77)
