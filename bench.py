@@ -434,7 +434,7 @@ def main():
                       if mode == "program" else "per-op: host schedule re-run every step, one launch per backend call")
     main_res = run_gpu_workload(args.workload, ntraj, args.steps, args.warmup, rank, world, local_rank, mode=mode)
     extra = {}
-    keep = ("ntraj_per_gpu", "dev_ms_per_step", "value", "e2e", "launches_per_step", "algo_bytes_per_step", "ops_per_step", "roofline", "kernels", "mode", "program", "log")
+    keep = ("cpu_baseline", "ntraj_per_gpu", "dev_ms_per_step", "value", "e2e", "launches_per_step", "algo_bytes_per_step", "ops_per_step", "roofline", "kernels", "mode", "program", "log")
     if world == 1 and mode == "program" and args.extras:
         try:  # the same workload through the per-call drop-in path, for comparison
             r = run_gpu_workload(args.workload, ntraj, max(2, min(args.steps, 3)), 3, 0, 1, local_rank, mode="per_op")
@@ -448,6 +448,11 @@ def main():
                                      mode="program" if WORKLOADS[name].get("program", WORKLOADS[name]["formalism"] == "clifford") else "per_op")
                 extra[name] = {k: r[k] for k in keep if k in r}
                 extra[name]["state_ops_per_sec"] = r["ops_per_step"] / (r["dev_ms_per_step"] * 1e-3)
+                per_core = max(1, cpu_sample_size(name) // 8) if cpu_sample_size(name) else 0
+                if per_core and not args.no_cpu:   # a short CPU sample of the same workload (oracle port), a few seconds per extra
+                    c = cpu_run(name, per_core)
+                    extra[name]["cpu_baseline"] = {"value": c["ntraj"] / c["wall"], "unit": "trajectories/s", "cores": c["cores"], "kind": "port",
+                                                   "sample": f"{per_core} full trajectories per core on {c['cores']} processes ({c['wall']:.1f} s wall)"}
             except Exception as e:  # an extra must never take the headline down
                 extra[name] = {"error": repr(e)[:300]}
     cpu = None
