@@ -328,6 +328,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dense_exec(DExecArgs a0) {
     DTile t;
     t.logT = a.logT; t.T = 1 << a.logT; t.G = THREADS >> a.logT;
     t.lane = threadIdx.x & (t.T - 1); t.grp = threadIdx.x >> a.logT;
+    const int pgrp = t.grp;
     t.gshift = (int)(threadIdx.x & 31u) & ~(t.T - 1);
     t.gmask = t.T == 32 ? 0xffffffffu : (((1u << t.T) - 1u) << t.gshift);
     t.arena = dsm;
@@ -354,6 +355,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dense_exec(DExecArgs a0) {
             }
             const DExecOp& op = sops[i % CHUNK];
             if (op.flags & 1) __syncthreads();
+            t.grp = (pgrp - (int)op.g0) & (t.G - 1);   // the op deals its items starting at group g0 (level scheduling)
             switch (op.type) {
             case DOP_CONST: {
                 const int L = 1 << (2 * op.n);
@@ -420,7 +422,7 @@ struct qsb_dprogram {
     qsb_ctx* ctx;
     DExecOp* d_ops; DExecOp* h_ops; int nops;
     double* d_aux; int naux;
-    int elems, nmasks, logT, blocks_per_sm, smem_bytes, barriers, threads, variant, aux_smem, regs;
+    int elems, nmasks, logT, blocks_per_sm, smem_bytes, barriers, threads, variant, aux_smem, regs, levels;
     uint64_t per_traj_rows, nstats;
 };
 
@@ -512,17 +514,44 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
         src.push_back((int)i);
         xops.push_back(x);
     }
+    // Level scheduling: the recorded order is the host's call order, but ops on different pairs (background noise of every
+    // idle pair at a time step, observables, the two halves of a swap) are independent.  Ops are re-ordered by their depth
+    // in the hazard graph (RAW / WAR / WAW on arena spans, mask words and the measurement scratch), so that the ops of one
+    // level run without barriers between them and spread over the groups of a block.  Draw ids and statistics rows are
+    // carried by the ops themselves, so the result does not depend on the order.  QSB_DEXEC_NOSCHED=1 keeps call order.
+    std::vector<int> level(xops.size(), 0);
+    if (!getenv("QSB_DEXEC_NOSCHED") && xops.size() > 1) {
+        std::vector<Access> accs(xops.size());
+        for (size_t j = 0; j < xops.size(); ++j) accs[j] = access_of(R->ops[src[j]]);
+        int nlev = 0;
+        for (size_t j = 0; j < xops.size(); ++j) {
+            int lv = 0;
+            for (size_t i = j; i-- > 0;) {
+                if (level[i] < lv) continue;   // cannot raise lv
+                if (overlap(accs[j].w, accs[i].r) || overlap(accs[j].w, accs[i].w) || overlap(accs[j].r, accs[i].w)) lv = level[i] + 1;
+            }
+            level[j] = lv; nlev = std::max(nlev, lv + 1);
+        }
+        std::vector<int> order(xops.size());
+        for (size_t j = 0; j < order.size(); ++j) order[j] = (int)j;
+        std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return level[x] < level[y]; });
+        std::vector<DExecOp> xo(xops.size()); std::vector<int> so(xops.size()), lo(xops.size());
+        for (size_t j = 0; j < order.size(); ++j) { xo[j] = xops[order[j]]; so[j] = src[order[j]]; lo[j] = level[order[j]]; }
+        xops.swap(xo); src.swap(so); level.swap(lo);
+        P->levels = nlev;
+    }
     P->nops = (int)xops.size(); P->naux = (int)aux.size(); P->nstats = R->stats_ptrs.size();
     // launch shape: T lanes per tile (32, 16 or 8) x block variant.  The executor is latency bound (a tile walks its op list
     // serially), so throughput follows the number of trajectories resident per SM: rank by resident trajectories, then by tile width.  QSB_DEXEC_T / QSB_DEXEC_THREADS pin the shape (tuning aid).
     int dev_smem = 0, sm_smem = 0;
     cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
     cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
-    const int NV = 5;
+    const int NV = 7;
     cudaFuncAttributes fa[NV];
-    const int vthreads[NV] = {256, 256, 128, 32, 32};
+    const int vthreads[NV] = {256, 256, 128, 32, 32, 512, 1024};
     const void* vfn[NV] = {(const void*)k_dense_exec<256, 1>, (const void*)k_dense_exec<256, 2>, (const void*)k_dense_exec<128, 4>,
-                           (const void*)k_dense_exec<32, 8>, (const void*)k_dense_exec<32, 16>};
+                           (const void*)k_dense_exec<32, 8>, (const void*)k_dense_exec<32, 16>, (const void*)k_dense_exec<512, 1>,
+                           (const void*)k_dense_exec<1024, 1>};
     for (int v = 0; v < NV; ++v)
         if (cudaFuncGetAttributes(&fa[v], vfn[v]) != cudaSuccess) { cudaGetLastError(); delete P; QSB_FAIL(QSB_ERR_CUDA, "k_dense_exec is not loadable on this device"); }
     const char *force_t = getenv("QSB_DEXEC_T"), *force_v = getenv("QSB_DEXEC_VARIANT");
@@ -532,6 +561,7 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
         const int T = 1 << logT;
         if (T > vthreads[v] || (vthreads[v] == 32 && T > 8)) continue;
         if ((force_t && atoi(force_t) != T) || (force_v && atoi(force_v) != v)) continue;
+        if (v >= 5 && !force_v) continue;   // the wide blocks (more warps per tile) are opt-in until measured on a workload
         size_t smem = (size_t)P->elems * T * sizeof(double2) + 2 * T * sizeof(double) + (size_t)(P->nmasks + 3) / 4 * 16 + (size_t)aux_smem * 8;
         smem = (smem + 15) / 16 * 16;
         if (smem + fa[v].sharedSizeBytes > (size_t)dev_smem) continue;
@@ -550,8 +580,24 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     P->aux_smem = aux_smem;
     {   // the single-group parts of ops (measurement decision, observables, random masks) rotate over the groups
         const int G = P->threads >> P->logT;
-        int rr = 0;
-        for (auto& x : xops) if (x.type == DOP_MEASURE || x.type == DOP_EXPECT || x.type == TOP_MASK_RANDOM) x.grp = (uint16_t)(rr++ % G);
+        // within a level the groups are dealt out round-robin: an op with fewer items than groups starts at the first group
+        // the previous op of the level left idle (g0), single-group parts (measurement decision, observables, random masks) take one group
+        int rr = 0, cur = -1;
+        for (size_t j = 0; j < xops.size(); ++j) {
+            DExecOp& x = xops[j];
+            if (level[j] != cur) { cur = level[j]; if (P->levels) rr = 0; }
+            int items = 0;
+            switch (x.type) {
+                case DOP_MEASURE: case DOP_EXPECT: case TOP_MASK_RANDOM: x.grp = (uint16_t)(rr % G); items = 1; break;
+                case DOP_CONST: case DOP_COPY: items = 1 << (2 * x.n); break;
+                case DOP_TENSOR: items = 1 << (2 * (x.n + x.n2)); break;
+                case DOP_APPLY: items = 1 << (2 * x.n - 2 * x.k); break;
+                case DOP_CHANNEL: case DOP_PTRACE: items = 1 << (2 * x.n - 2); break;
+                default: break;
+            }
+            if (items > 1 && P->levels) x.g0 = (uint8_t)(rr % G);
+            rr += std::min(items, G);
+        }
         // barrier before an op when it touches storage an op since the last barrier wrote (or writes what one read); the
         // op-chunk refill of the chosen block variant is a barrier already
         const int chunk = QSB_DEXEC_CHUNK_OF(P->threads);
@@ -579,8 +625,8 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     for (int v = 0; v < NV && rc == QSB_OK; ++v)
         if (cudaFuncSetAttribute(vfn[v], cudaFuncAttributeMaxDynamicSharedMemorySize, dev_smem - (int)fa[v].sharedSizeBytes) != cudaSuccess) rc = QSB_ERR_CUDA;
     if (rc != QSB_OK) { if (rc == QSB_ERR_CUDA) { qsb_set_error("dense program upload failed: %s", cudaGetErrorString(cudaGetLastError())); } qsb_dexec_free(P); return rc; }
-    if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] dense program: %d ops, %d barriers, %d elements, %d mask words, %d aux doubles (%s), T=%d, %d threads, %d block(s)/SM, %d B smem, %d regs\n",
-                                         P->nops, P->barriers, P->elems, P->nmasks, P->naux, P->aux_smem ? "smem" : "global", 1 << P->logT, P->threads, P->blocks_per_sm, P->smem_bytes, P->regs);
+    if (getenv("QSB_REC_TRACE")) fprintf(stderr, "[rec] dense program: %d ops, %d levels, %d barriers, %d elements, %d mask words, %d aux doubles (%s), T=%d, %d threads, %d block(s)/SM, %d B smem, %d regs\n",
+                                         P->nops, P->levels, P->barriers, P->elems, P->nmasks, P->naux, P->aux_smem ? "smem" : "global", 1 << P->logT, P->threads, P->blocks_per_sm, P->smem_bytes, P->regs);
     *out = P;
     return QSB_OK;
 }
@@ -598,6 +644,8 @@ int qsb_dexec_run(qsb_dprogram* P, uint64_t traj_shift, uint64_t draw_base) {
     else if (P->variant == 1) k_dense_exec<256, 2><<<(unsigned)blocks, 256, P->smem_bytes, ctx->stream>>>(a);
     else if (P->variant == 2) k_dense_exec<128, 4><<<(unsigned)blocks, 128, P->smem_bytes, ctx->stream>>>(a);
     else if (P->variant == 3) k_dense_exec<32, 8><<<(unsigned)blocks, 32, P->smem_bytes, ctx->stream>>>(a);
+    else if (P->variant == 5) k_dense_exec<512, 1><<<(unsigned)blocks, 512, P->smem_bytes, ctx->stream>>>(a);
+    else if (P->variant == 6) k_dense_exec<1024, 1><<<(unsigned)blocks, 1024, P->smem_bytes, ctx->stream>>>(a);
     else k_dense_exec<32, 16><<<(unsigned)blocks, 32, P->smem_bytes, ctx->stream>>>(a);
     QSB_LAUNCH_CHECK(ctx);
     // compulsory HBM traffic of the fused launch: op list + constants once, statistics and per-trajectory rows written once

@@ -30,7 +30,7 @@ struct DExecOp {              // 80 bytes (five 16-byte words: staged through sh
     uint32_t fpow;                   // DOP_EXPECT: the value is multiplied by i^fpow (sign and the i^ny of a Pauli string)
     double* stats;                   // absolute device pointers captured at record time
     double* per_traj;
-    uint64_t reserved1;
+    uint8_t g0, reserved0[7];        // level scheduling: the op deals its items to the groups starting at group g0
 };
 static_assert(sizeof(DExecOp) == 80, "DExecOp layout");
 #define QSB_DEXEC_CHUNK_OF(threads) ((threads) >= 128 ? 32 : 8)   // ops staged per shared-memory refill (80 B each, per block)
