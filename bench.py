@@ -36,7 +36,11 @@ def wl_fgr(make_repr, formalism, record):
     from qsb200.workloads import firstgenrepeater as fgr
     bg = S.Depolarization(100.0) if formalism == "clifford" else S.T1T2Noise(1000.0, 100.0)
     from qsb200.registers import dispose
-    _, _, net = fgr.monte_carlo_trajectory(make_repr, background=bg, record=record, **FGR)
+    kw = dict(FGR)
+    if formalism == "mc":   # a mixture would be lowered to a density matrix (express of a mixed state): pure pairs keep the states kets
+        from qsb200 import ops
+        kw["noisy_pair"] = ops.StabilizerState("XX ZZ")
+    _, _, net = fgr.monte_carlo_trajectory(make_repr, background=bg, record=record, **kw)
     dispose(net.registers)
     return net.log
 
@@ -93,6 +97,8 @@ WORKLOADS = {
                                       desc="examples/firstgenrepeater_lowlevel, sizes [2,3,4,3,2], F=0.97, CliffordRepr, Depolarization(100), t=0:0.2:25"),
     "firstgenrepeater_dm": dict(fn=wl_fgr, formalism="qo", ntraj=1_000_000, program=True,
                                 desc="examples/firstgenrepeater_lowlevel, sizes [2,3,4,3,2], F=0.97, QuantumOpticsRepr dm, T1T2Noise(1000,100), t=0:0.2:25"),
+    "firstgenrepeater_mcket": dict(fn=wl_fgr, formalism="mc", ntraj=1_000_000, program=False,
+                                   desc="examples/firstgenrepeater_lowlevel, sizes [2,3,4,3,2], perfect pairs, QuantumMCRepr kets, T1T2Noise(1000,100) as sampled Kraus jumps, t=0:0.2:25"),
     "ghz_sensors_dm": dict(fn=wl_ghz, formalism="qo", ntraj=16384,
                            desc="examples/distributed_ghz_sensors F-TMBL trial, S=4 all links up (peak 8-qubit dm = 1 MiB per trajectory), F=0.99, Depolarization(1.0); "
                                 "10^6 trajectories = 62 steps of 16384 resident trajectories"),
@@ -142,7 +148,7 @@ def cpu_run(workload, per_core, cores=None):
 
 
 def cpu_sample_size(workload):
-    return {"firstgenrepeater_clifford": 60, "firstgenrepeater_dm": 100, "sweep12_dm": 0, "ghz_sensors_dm": 2, "repeatergrid_clifford": 40}.get(workload, 20)
+    return {"firstgenrepeater_clifford": 60, "firstgenrepeater_dm": 100, "firstgenrepeater_mcket": 100, "sweep12_dm": 0, "ghz_sensors_dm": 2, "repeatergrid_clifford": 40}.get(workload, 20)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -399,7 +405,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="firstgenrepeater_clifford", choices=sorted(WORKLOADS))
     ap.add_argument("--ntraj", type=int, default=0, help="trajectories per GPU (default: the config's)")
-    ap.add_argument("--extras", default="firstgenrepeater_dm,ghz_sensors_dm,repeatergrid_clifford,sweep12_dm", help="extra workloads reported under 'extra' (N=1 only)")
+    ap.add_argument("--extras", default="firstgenrepeater_dm,firstgenrepeater_mcket,ghz_sensors_dm,repeatergrid_clifford,sweep12_dm", help="extra workloads reported under 'extra' (N=1 only)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--mode", default="auto", choices=["auto", "per_op", "program"],
                     help="program: recorded op list replayed as one fused launch (Clifford workloads); per_op: one launch per backend call")

@@ -146,6 +146,8 @@ def purifier(net, nodea, nodeb, wait_time, busy_time):
         success = circuit(rega[p1a], regb[p1b], rega[p2a], regb[p2b])
         follow_success = bool(success) if isinstance(success, bool) or getattr(getattr(success, "ctx", None), "ntraj", 2) == 1 else True
         if not follow_success:
+            net.log["failures"] = net.log.get("failures", 0) + 1          # single-trajectory runs only (the twin of a lane)
+            net.log.setdefault("first_failure_time", sim.now)
             _release_pair_tracking(net, nodea, p1a)
             _release_pair_tracking(net, nodeb, p1b)
         else:
