@@ -190,6 +190,16 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm)}
 
 
+def ncu_traffic(workload, ntraj, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture of this exact
+    workload / size / kernel (profiles/ncu_traffic.json), or None when there is no capture for it."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f).get(f"{workload}|{ntraj}|{kernel}")
+    except Exception:
+        return None
+
+
 def measured_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -371,8 +381,10 @@ def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, pr
             sec = sum(r["ms"] for r in fused) * 1e-3 / max(1, fused[0]["launches"])
             hbm = sum(r["algo_bytes"] for r in fused) / max(1, fused[0]["launches"])
             gbs = info["table_bytes"] / sec / 1e9
-            out["roofline"] = {"bound": "hbm", "kernel": "+".join(sorted(r["kernel"] for r in fused)), "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
-                               "traffic": None, "peak_source": which, "algo_bytes_per_launch": info["table_bytes"], "us_per_launch": sec * 1e6,
+            kname = "+".join(sorted(r["kernel"] for r in fused))
+            traffic = ncu_traffic(workload, ntraj, kname)
+            out["roofline"] = {"bound": "hbm", "kernel": kname, "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                               "traffic": traffic["bytes"] if traffic else None, "traffic_source": traffic["source"] if traffic else None, "peak_source": which, "algo_bytes_per_launch": info["table_bytes"], "us_per_launch": sec * 1e6,
                                "share_of_step": sum(r["share"] for r in fused),
                                "fused_hbm_bytes_per_launch": hbm, "fused_hbm_gbs": hbm / sec / 1e9,
                                "note": ("algorithmic bytes = SURVEY 8d table bytes of the recorded ops (per-op accounting of the same op list); the fused run keeps "

@@ -478,6 +478,8 @@ static int launch_rdm1(qsb_state* st, int q, int* nsplit_out) {
     if (st->kind == QSB_DM) k_rdm1<true><<<grid, TPB, 0, ctx->stream>>>((const double2*)st->data, ctx->npad, st->n, q, range, nsplit, ctx->scratch);
     else k_rdm1<false><<<grid, TPB, 0, ctx->stream>>>((const double2*)st->data, ctx->npad, st->n, q, range, nsplit, ctx->scratch);
     QSB_LAUNCH_CHECK(ctx);
+    // reads the ket once (dm: the three touched entries of each 2x2 block of qubit q on the diagonal), writes 4 partial sums per split
+    qsb_account(ctx, "k_rdm1", ((uint64_t)16 * (st->kind == QSB_DM ? 3 * range : 2 * range) + (uint64_t)32 * nsplit) * ctx->ntraj);
     *nsplit_out = nsplit;
     return QSB_OK;
 }
