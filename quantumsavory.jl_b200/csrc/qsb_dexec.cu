@@ -532,6 +532,26 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
             }
             level[j] = lv; nlev = std::max(nlev, lv + 1);
         }
+        if (getenv("QSB_REC_TRACE")) {   // how long would the chain be without storage reuse?  (tuning aid)
+            auto depth = [&](bool raw_only, bool skip_small) {
+                auto filt = [&](const std::vector<Span>& v) { std::vector<Span> o; for (auto& x : v) if (!skip_small || x.lo < SCR) o.push_back(x); return o; };
+                std::vector<int> lv(xops.size(), 0); int d = 0;
+                std::vector<Access> fa(xops.size());
+                for (size_t j = 0; j < xops.size(); ++j) { fa[j].r = filt(accs[j].r); fa[j].w = filt(accs[j].w); }
+                for (size_t j = 0; j < xops.size(); ++j) {
+                    int l = 0;
+                    for (size_t i = j; i-- > 0;) {
+                        if (lv[i] < l) continue;
+                        bool dep = overlap(fa[j].r, fa[i].w) || (!raw_only && (overlap(fa[j].w, fa[i].r) || overlap(fa[j].w, fa[i].w)));
+                        if (dep) l = lv[i] + 1;
+                    }
+                    lv[j] = l; d = std::max(d, l + 1);
+                }
+                return d;
+            };
+            fprintf(stderr, "[rec] dense hazard-graph depth: %d (all hazards), %d (ignoring mask words and scratch), %d (true dependencies only), %d (true, ignoring masks/scratch)\n",
+                    nlev, depth(false, true), depth(true, false), depth(true, true));
+        }
         std::vector<int> order(xops.size());
         for (size_t j = 0; j < order.size(); ++j) order[j] = (int)j;
         std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return level[x] < level[y]; });
