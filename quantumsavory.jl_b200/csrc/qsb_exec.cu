@@ -7,9 +7,11 @@
 // one thread can run the complete op list on its column.  The arena (all live states and masks of the
 // schedule, planes allocated/recycled at record time) is a [planes][blockDim] tile of shared memory.
 //
-// Lanes per thread: this translation unit compiles the tableau core with 8-lane BYTE planes (QSB_PLANE_T), so an
-// ensemble of N trajectories runs on N/8 threads instead of N/32 -- the bit logic is latency bound (dependent
-// shared-memory round trips), and 10^6 trajectories are only 977 warps of 32-lane words on 148 SMs.
+// Lanes per thread (QSB_EXEC_PLANE_T): the executor is bound by the dependent shared-memory round trips of each op and by
+// how many trajectories' tableaux fit in an SM's shared memory, so its run time barely depends on the plane width
+// (8-lane bytes: 24 warps per SM at 0.54 issue utilisation, 3.52 ms; 32-lane words: 6 warps per SM and a quarter of the
+// instructions, 3.23 ms per 10^6 firstgenrepeater trajectories).  Words are the default; -DQSB_EXEC_PLANE_T=uint8_t|uint16_t
+// builds the narrower variants (QSB200_LIB selects such a build at run time).
 #include <limits.h>
 #include <math.h>
 #include <algorithm>

@@ -15,8 +15,8 @@
 #endif
 #define MAXN QSB_TAB_MAXN
 // Storage type of one bit plane element: the number of trajectories ("lanes") one thread advances.  The per-op
-// kernels use 32-lane words; the fused executor (qsb_exec.cu) compiles this header with 8-lane bytes to get 4x
-// the threads out of the same ensemble.  Arithmetic is always done in 32-bit registers; QSB_FULL masks the lanes.
+// kernels use 32-lane words; the fused executor (qsb_exec.cu) can compile this header with narrower planes (more threads
+// out of the same ensemble; see qsb_exec.cu).  Arithmetic is always done in 32-bit registers; QSB_FULL masks the lanes.
 #ifndef QSB_PLANE_T
 #define QSB_PLANE_T uint32_t
 #define QSB_CORE_NS tabcore32
