@@ -37,6 +37,7 @@ struct qsb_program {
     qsb_ctx* ctx;
     qsb_dprogram* dprog;   // non-null: a dense program (qsb_dexec.cu); the tableau fields below are unused except d_stats
     DrawSpec* d_specs; int nspecs, nslots, slot_stride;
+    int dyn;               // 1: k_tab_exec<1> with `threads` as its run-time block size
     uint8_t* d_aux; int naux, nfolded;   // constant tables of folded ops
     uint32_t* bits;        // [nwords][slot_stride] decision words written by k_draw_bits, read by k_tab_exec
     ExecOp* d_ops; int nops;
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(256) k_draw_bits(const DrawSpec* __restrict__ 
 // the per-block-size instantiations live in qsb_exec_inst.cu (one object per size, csrc/Makefile)
 #define QSB_EXEC_SIZES(X) X(32) X(64) X(96) X(128) X(256)
 #define X(T) cudaError_t qsb_exec_launch_##T(const ExecArgs&, unsigned, int, cudaStream_t);
-QSB_EXEC_SIZES(X) X(0)
+QSB_EXEC_SIZES(X) X(0) X(1)
 #undef X
 const int qsb_exec_block_sizes[] = {
 #define X(T) T,
@@ -221,7 +222,7 @@ const int qsb_exec_block_sizes[] = {
 qsb_exec_launch_fn qsb_exec_launcher(int threads) {
     switch (threads) {
 #define X(T) case T: return qsb_exec_launch_##T;
-        QSB_EXEC_SIZES(X) X(0)
+        QSB_EXEC_SIZES(X) X(0) X(1)
 #undef X
         default: return nullptr;
     }
@@ -481,6 +482,35 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
         int rank = (per_sm >= 2 ? 1000 : 0) + t;
         if (rank > best_rank) { best_rank = rank; best_t = t; }
     }
+    // Whole waves.  A block runs for (ops x latency of an op body) whatever its width, and the tile capacity of an SM fixes how many
+    // lane groups are resident, so a small tail wave costs as much as a full one (10^6 firstgenrepeater trajectories on 96-thread
+    // blocks: 1.1 waves, 3.22 ms; 909 312 trajectories, exactly one wave: 1.67 ms).  The run-time sized variant (k_tab_exec<1>, any
+    // block size up to 256, partial warps allowed) spreads the lane groups evenly over the fewest waves that fit.
+    P->dyn = 0;
+    if (force_t && !best_t && atoi(force_t) >= 32 && atoi(force_t) <= 256 && (size_t)P->planes * atoi(force_t) * sizeof(plane_t) <= (size_t)dev_smem) { best_t = atoi(force_t); P->dyn = 1; }
+    else if (best_t && !force_t && !getenv("QSB_EXEC_NODYN")) {
+        int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+        int sm_smem = 0; cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
+        const size_t per_thread = (size_t)P->planes * sizeof(plane_t), fixed = 1024 + QSB_EXEC_CHUNK * sizeof(ExecOp);
+        auto waves_of = [&](int t, int per_sm) { long blocks = (groups + t - 1) / t; return (blocks + (long)sms * per_sm - 1) / ((long)sms * per_sm); };
+        const int fixed_per_sm = std::max(1, (int)((size_t)sm_smem / (per_thread * best_t + fixed)));
+        long best_w = waves_of(best_t, fixed_per_sm);
+        int dyn_t = 0;
+        const int force_b = getenv("QSB_EXEC_BLOCKS_PER_SM") ? atoi(getenv("QSB_EXEC_BLOCKS_PER_SM")) : 0;   // tuning aid
+        for (long w = 1; w < best_w || (force_b && w <= best_w); ++w) {
+            for (int b = 1; b <= 8 && !dyn_t; ++b) {
+                if (force_b && b != force_b) continue;
+                long tmax = ((long)sm_smem / b - (long)fixed) / (long)per_thread;
+                if (tmax > 256) tmax = 256;
+                if ((size_t)tmax * per_thread > (size_t)dev_smem) tmax = dev_smem / per_thread;
+                long need = (groups + (long)sms * b * w - 1) / ((long)sms * b * w);
+                if (need < 32) need = 32;
+                if (need <= tmax && waves_of((int)need, b) <= w) dyn_t = (int)need;
+            }
+            if (dyn_t) break;
+        }
+        if (dyn_t) { best_t = dyn_t; P->dyn = 1; }
+    }
     if (best_t) { P->threads = best_t; P->smem_bytes = P->planes * best_t * (int)sizeof(plane_t); P->arena = nullptr; }
     else {
         P->threads = 128; P->smem_bytes = 0;
@@ -522,7 +552,8 @@ extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t dra
     unsigned blocks = (unsigned)((a.W + P->threads - 1) / P->threads);
     QSB_PRE(ctx, "k_tab_exec");
     {
-        qsb_exec_launch_fn launch = qsb_exec_launcher(P->arena ? 0 : P->threads);
+        qsb_exec_launch_fn launch = qsb_exec_launcher(P->arena ? 0 : (P->dyn ? 1 : P->threads));
+        a.dyn_threads = P->threads;
         if (!launch) QSB_FAIL(QSB_ERR_BAD_ARG, "no executor compiled for %d threads per block", P->threads);
         cudaError_t e = launch(a, blocks, P->smem_bytes, ctx->stream);
         if (e != cudaSuccess) QSB_FAIL(QSB_ERR_CUDA, "k_tab_exec launch failed: %s", cudaGetErrorString(e));

@@ -12,13 +12,15 @@
 
 // T > 0: the arena is a [planes][T] tile of shared memory (block of T threads, compile-time stride);
 // T == 0: the arena is in global memory with stride a.W (programs whose tile exceeds the shared memory of an SM).
+// T == 1: shared-memory tile whose stride is the RUN-TIME block size (any thread count up to 256, partial warps allowed), so the host
+// can size the blocks to cover the ensemble in whole waves (qsb_exec.cu: a 9 % tail wave used to double the run time).
 template <int T>
-__global__ void __launch_bounds__(T ? T : 128) k_tab_exec(ExecArgs a) {
+__global__ void __launch_bounds__(T > 1 ? T : (T == 1 ? 256 : 128)) k_tab_exec(ExecArgs a) {
     extern __shared__ plane_t tile[];
     const size_t wg = blockIdx.x * (size_t)blockDim.x + threadIdx.x;  // global lane group (trajectories QSB_LANES*wg ..)
     const bool on = wg < a.W;
     plane_t* const base = T ? tile : a.arena;
-    const size_t W = T ? (size_t)T : a.W;
+    const size_t W = T > 1 ? (size_t)T : (T == 1 ? (size_t)blockDim.x : a.W);
     const size_t w = T ? (size_t)threadIdx.x : (on ? wg : 0);
     const uint32_t validw = on ? a.valid[wg] : 0u;
 #define PL(idx) (base + (size_t)(idx) * W)
@@ -141,10 +143,11 @@ __global__ void __launch_bounds__(T ? T : 128) k_tab_exec(ExecArgs a) {
                 }
             }
             if (op.stats) {  // whole warps reach this point together (the op list is uniform)
-                n_alive = __reduce_add_sync(0xffffffffu, n_alive);
-                num = __reduce_add_sync(0xffffffffu, num);
-                num2 = __reduce_add_sync(0xffffffffu, num2);
-                nelem = __reduce_max_sync(0xffffffffu, nelem);
+                const unsigned am = __activemask();   // the last warp of a run-time sized block may be partial
+                n_alive = __reduce_add_sync(am, n_alive);
+                num = __reduce_add_sync(am, num);
+                num2 = __reduce_add_sync(am, num2);
+                nelem = __reduce_max_sync(am, nelem);
                 if ((threadIdx.x & 31) == 0 && n_alive) {
                     const double inv = 1.0 / (double)nelem;   // nelem = 2^k: the scaled tallies are exact
                     atomicAdd(&op.stats[0], (double)n_alive); atomicAdd(&op.stats[1], (double)num * inv); atomicAdd(&op.stats[2], (double)num2 * inv * inv);
@@ -195,6 +198,6 @@ cudaError_t QSB_CAT(qsb_exec_launch_, QSB_EXEC_T)(const ExecArgs& a, unsigned bl
         if (e != cudaSuccess) return e;
         configured = smem_bytes;
     }
-    k_tab_exec<QSB_EXEC_T><<<blocks, QSB_EXEC_T ? QSB_EXEC_T : 128, smem_bytes, stream>>>(a);
+    k_tab_exec<QSB_EXEC_T><<<blocks, QSB_EXEC_T > 1 ? QSB_EXEC_T : (QSB_EXEC_T == 1 ? a.dyn_threads : 128), smem_bytes, stream>>>(a);
     return cudaGetLastError();
 }

@@ -35,6 +35,7 @@ struct ExecArgs {
     const plane_t* valid;
     size_t W;                 // lane groups (threads) in the ensemble = trajectories / QSB_LANES
     uint64_t seed, traj0, draw_base;
+    int dyn_threads;          // block size of the run-time sized variant (k_tab_exec<1>)
 };
 
 // launchers, one per compiled block size (0 = arena in global memory)
