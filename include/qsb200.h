@@ -80,6 +80,9 @@ int qsb_ctx_destroy(qsb_ctx* ctx);
 int qsb_ctx_set_stream(qsb_ctx* ctx, void* cuda_stream);
 int qsb_ctx_sync(qsb_ctx* ctx); /* host-visible: waits, then reports sticky device-side errors (QSB_ERR_NOT_NORMALIZED) */
 int64_t qsb_ctx_ntraj(const qsb_ctx* ctx);
+/* re-bases the context on the global trajectory ids [traj_offset, traj_offset+ntraj): the next batch of the same
+ * schedule (the replicate loop of 6.1_compare_formalisms_noplot.jl:66-73) without re-creating the context */
+int qsb_ctx_set_traj_offset(qsb_ctx* ctx, int64_t traj_offset);
 /* counters[0]=kernel launches, [1]=algorithmic bytes (SURVEY 8d table x trajectories), [2]=state ops x trajectories, [3]=draw ids consumed */
 int qsb_ctx_counters(const qsb_ctx* ctx, uint64_t counters[4]);
 int qsb_ctx_reset_counters(qsb_ctx* ctx);
@@ -167,10 +170,10 @@ int qsb_state_kill(qsb_state* st, const qsb_mask* lanes);
  * Between qsb_record_begin and qsb_record_end every call on the context is CAPTURED instead of launched
  * (like a CUDA graph capture): handles created inside are virtual, host-visible calls (counts_host,
  * stats_host, *_to_host, qsb_mask_count) are refused, and device pointers passed as stats_dev /
- * per_traj_dev are captured by address.  Only Clifford (QSB_TAB) states can be recorded in this round.
- * qsb_program_run executes the whole op list in ONE launch with each 32-trajectory word's tableaux
- * resident in shared memory (a thread only ever touches its own word column, so no grid sync is needed
- * between ops).  traj_shift re-bases the ensemble on fresh global trajectory ids (a new batch of the same
+ * per_traj_dev are captured by address.  A program holds tableau (QSB_TAB) states or dense (KET/DM) states, never both;
+ * MCKET trajectory kets are refused.  qsb_program_run executes the whole op list as ONE fused pass: tableau programs with
+ * each 32-trajectory word's tableaux resident in shared memory (a thread only ever touches its own word column, so no
+ * grid sync is needed between ops), dense programs with every live density matrix of a 32-trajectory tile in shared memory.  traj_shift re-bases the ensemble on fresh global trajectory ids (a new batch of the same
  * schedule); draw_base offsets every draw id.  SURVEY.md 7.2 "command buffer", 8f-2. */
 typedef struct qsb_program qsb_program;
 int qsb_record_begin(qsb_ctx* ctx);

@@ -69,6 +69,7 @@ def _declare(L):
         "qsb_ctx_set_stream": (C.c_int, [vp, vp]),
         "qsb_ctx_sync": (C.c_int, [vp]),
         "qsb_ctx_ntraj": (C.c_int64, [vp]),
+        "qsb_ctx_set_traj_offset": (C.c_int, [vp, C.c_int64]),
         "qsb_ctx_counters": (C.c_int, [vp, u64p]),
         "qsb_ctx_reset_counters": (C.c_int, [vp]),
         "qsb_ctx_profile": (C.c_int, [vp, C.c_int]),

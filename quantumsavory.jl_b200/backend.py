@@ -44,6 +44,7 @@ class BatchContext:
         self.traj_offset = traj_offset
         self.device = device
         self._draw = 0
+        self.recording = False
 
     def next_draw(self) -> int:
         d = self._draw
@@ -52,6 +53,11 @@ class BatchContext:
 
     def sync(self):
         check(self.L.qsb_ctx_sync(self.p))
+
+    def set_traj_offset(self, traj_offset: int):
+        """The next batch of the same schedule: global trajectory ids [traj_offset, traj_offset + ntraj)."""
+        check(self.L.qsb_ctx_set_traj_offset(self.p, int(traj_offset)))
+        self.traj_offset = int(traj_offset)
 
     def counters(self):
         c = (C.c_uint64 * 4)()
@@ -133,10 +139,12 @@ class _Recording:
 
     def __enter__(self):
         check(self.ctx.L.qsb_record_begin(self.ctx.p))
+        self.ctx.recording = True
         return self
 
     def __exit__(self, et, ev, tb):
         p = C.c_void_p()
+        self.ctx.recording = False
         rc = self.ctx.L.qsb_record_end(self.ctx.p, C.byref(p))
         if et is None:
             check(rc)

@@ -97,6 +97,7 @@ extern "C" int qsb_ctx_profile_report(qsb_ctx* ctx, char* buf, size_t buflen) {
 // ---------------------------------------------------------------------------------------------
 int qsb_dev_alloc(qsb_ctx* ctx, void** p, size_t bytes) {
     if (bytes == 0) bytes = 16;
+    qsb_use_device(ctx);
     cudaError_t e = cudaMallocAsync(p, bytes, ctx->stream);
     if (e == cudaErrorMemoryAllocation) {
         // the pool keeps freed blocks (release threshold = max): wait for pending frees, give them back, retry once
@@ -117,6 +118,7 @@ int qsb_dev_alloc(qsb_ctx* ctx, void** p, size_t bytes) {
 }
 int qsb_dev_free(qsb_ctx* ctx, void* p) {
     if (!p) return QSB_OK;
+    qsb_use_device(ctx);
     QSB_CUDA(cudaFreeAsync(p, ctx->stream));
     return QSB_OK;
 }
@@ -323,6 +325,7 @@ extern "C" int qsb_ctx_set_stream(qsb_ctx* ctx, void* s) {
 }
 extern "C" int qsb_ctx_sync(qsb_ctx* ctx) {
     if (!ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "null context");
+    qsb_use_device(ctx);
     int flags[4];
     QSB_CUDA(cudaMemcpyAsync(flags, ctx->dev_flags, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
     QSB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -333,6 +336,12 @@ extern "C" int qsb_ctx_sync(qsb_ctx* ctx) {
     return QSB_OK;
 }
 extern "C" int64_t qsb_ctx_ntraj(const qsb_ctx* ctx) { return ctx ? ctx->ntraj : 0; }
+extern "C" int qsb_ctx_set_traj_offset(qsb_ctx* ctx, int64_t traj_offset) {
+    if (!ctx || traj_offset < 0) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_ctx_set_traj_offset: bad argument");
+    if (ctx->rec) QSB_FAIL(QSB_ERR_BAD_ARG, "the trajectory ids cannot change inside a recording (use traj_shift of qsb_program_run)");
+    ctx->traj_offset = traj_offset;   // kernels read it at launch: stream order keeps earlier launches on the old ids
+    return QSB_OK;
+}
 extern "C" int qsb_ctx_counters(const qsb_ctx* ctx, uint64_t c[4]) {
     if (!ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "null context");
     c[0] = ctx->launches; c[1] = ctx->algo_bytes; c[2] = ctx->ops; c[3] = ctx->draws;

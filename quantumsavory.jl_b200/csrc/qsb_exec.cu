@@ -326,6 +326,7 @@ extern "C" int qsb_record_begin(qsb_ctx* ctx) {
 extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     if (!ctx || !out) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
     if (!ctx->rec) QSB_FAIL(QSB_ERR_BAD_ARG, "not recording");
+    qsb_use_device(ctx);
     qsb_recorder* R = ctx->rec;
     qsb_program* P = new qsb_program();
     memset(P, 0, sizeof(*P));
@@ -528,6 +529,7 @@ extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t dra
     if (!P) QSB_FAIL(QSB_ERR_BAD_ARG, "null program");
     qsb_ctx* ctx = P->ctx;
     if (ctx->rec) QSB_FAIL(QSB_ERR_BAD_ARG, "cannot run a program while recording");
+    qsb_use_device(ctx);
     if (P->nstats) {
         QSB_PRE(ctx, "k_zero_stats");
         k_zero_stats<<<(P->nstats + 127) / 128, 128, 0, ctx->stream>>>(P->d_stats, P->nstats);

@@ -143,7 +143,10 @@ __global__ void __launch_bounds__(T > 1 ? T : (T == 1 ? 256 : 128)) k_tab_exec(E
                 }
             }
             if (op.stats) {  // whole warps reach this point together (the op list is uniform)
-                const unsigned am = __activemask();   // the last warp of a run-time sized block may be partial
+                // the last warp of a run-time sized block may be partial: the member mask follows from the block geometry
+                // (__activemask() would only report who happens to be converged here, and a split warp would drop tallies)
+                const unsigned wbase = threadIdx.x & ~31u, wthreads = blockDim.x - wbase;
+                const unsigned am = wthreads >= 32u ? 0xffffffffu : ((1u << wthreads) - 1u);
                 n_alive = __reduce_add_sync(am, n_alive);
                 num = __reduce_add_sync(am, num);
                 num2 = __reduce_add_sync(am, num2);
@@ -192,11 +195,14 @@ __global__ void __launch_bounds__(T > 1 ? T : (T == 1 ? 256 : 128)) k_tab_exec(E
 #define QSB_CAT2(a, b) a##b
 #define QSB_CAT(a, b) QSB_CAT2(a, b)
 cudaError_t QSB_CAT(qsb_exec_launch_, QSB_EXEC_T)(const ExecArgs& a, unsigned blocks, int smem_bytes, cudaStream_t stream) {
-    static int configured = -1;
-    if (smem_bytes > configured) {
+    // the opt-in is per device (and per function): remember it for the device that is current for this launch
+    static int configured[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || smem_bytes > configured[dev]) {
         cudaError_t e = cudaFuncSetAttribute(k_tab_exec<QSB_EXEC_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
         if (e != cudaSuccess) return e;
-        configured = smem_bytes;
+        if (dev >= 0 && dev < 64) configured[dev] = smem_bytes;
     }
     k_tab_exec<QSB_EXEC_T><<<blocks, QSB_EXEC_T > 1 ? QSB_EXEC_T : (QSB_EXEC_T == 1 ? a.dyn_threads : 128), smem_bytes, stream>>>(a);
     return cudaGetLastError();

@@ -73,6 +73,10 @@ struct qsb_mask {
     int gen;
 };
 
+// Several contexts on different GPUs may live in one process (the Julia glue drives 8 shards from one host loop):
+// every path that allocates, launches or copies first makes the context's device current for the calling thread.
+static inline void qsb_use_device(const qsb_ctx* ctx) { int cur = -1; if (cudaGetDevice(&cur) != cudaSuccess || cur != ctx->device) cudaSetDevice(ctx->device); }
+
 // ---- error plumbing ---------------------------------------------------------------------------
 void qsb_set_error(const char* fmt, ...);
 #define QSB_FAIL(code, ...) do { qsb_set_error(__VA_ARGS__); return (code); } while (0)
@@ -83,7 +87,7 @@ void qsb_set_error(const char* fmt, ...);
 #define QSB_LAUNCH_CHECK(ctx) do { (ctx)->launches++; if ((ctx)->prof) qsb_prof_post(ctx); cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { \
     qsb_set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(e_), __FILE__, __LINE__); return QSB_ERR_CUDA; } } while (0)
 // brackets the next launch with CUDA events on the context's stream when profiling is on
-#define QSB_PRE(ctx, name) do { if ((ctx)->prof) qsb_prof_pre(ctx, name); } while (0)
+#define QSB_PRE(ctx, name) do { qsb_use_device(ctx); if ((ctx)->prof) qsb_prof_pre(ctx, name); } while (0)
 void qsb_prof_pre(qsb_ctx* ctx, const char* kernel);
 void qsb_prof_post(qsb_ctx* ctx);
 // adds an op's algorithmic bytes (SURVEY 8d table x trajectories) to the context total and to `kernel`'s row

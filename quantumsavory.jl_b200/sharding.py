@@ -31,6 +31,8 @@ class StatsBuffer:
         self.k = k
 
     def slot_ptr(self, i: int) -> int:
+        if not 0 <= i < self.k:     # the device kernels write through this pointer: never hand out a row past the end
+            raise IndexError(f"statistics row {i} requested from a StatsBuffer of {self.k} rows")
         return self.t.data_ptr() + i * 32
 
     def allreduce(self):

@@ -309,6 +309,49 @@ def doctest_values(env):
         apply(reg[1], X, time=5)  # src/baseops/apply.jl:12-14
 
 
+# noninstant_and_backgrounds_qubit_tests.jl:8-20 (time bookkeeping) + src/noninstant.jl:9-13 (apply! then uptotime!) ---
+def noninstant_gate(env):
+    from qsb200.ops import H
+    from qsb200.registers import NonInstantGate
+    for f in ("qo", "clifford"):
+        reg = Register(2, env.repr(f))
+        initialize(reg[1]); initialize(reg[2])
+        uptotime(reg[1], 0.2)
+        uptotime(reg[1], 0.2)
+        with pytest.raises(RuntimeError, match="simulation time is higher"):
+            uptotime(reg[1], 0.1)
+        apply(reg[1], H, time=0.3)
+        _, t1 = apply(reg[1], NonInstantGate(H, 0.1), time=0.4)
+        assert abs(t1 - 0.5) < 1e-15 and reg.accesstimes[0] == t1
+        _, t2 = apply((reg[1], reg[2]), NonInstantGate(CNOT, 0.1))
+        assert abs(t2 - 0.6) < 1e-15 and reg.accesstimes == [t2, t2]
+        with pytest.raises(RuntimeError, match="simulation time is higher"):
+            uptotime(reg[1], 0.55)
+        with pytest.raises(RuntimeError, match="simulation time is higher"):
+            apply(reg[1], H, time=0.55)
+        approx(env, observable(reg[1:2], tensor(Z, Z)), 1.0)      # H.H = 1, CNOT|00> = |00>, no background
+    # the gate followed by waiting under a background == the two calls made by hand (density matrices: deterministic)
+    for bg in (S.T1Decay(1.0), S.T2Dephasing(0.7), S.T1T2Noise(1.0, 0.8), S.Depolarization(2.0)):
+        a, b = Register(2, env.repr("qo"), bg), Register(2, env.repr("qo"), bg)
+        for r in (a, b):
+            initialize(r[1], S.X1); initialize(r[2])
+        apply(a[1], NonInstantGate(H, 0.25), time=0.1)
+        apply((a[1], a[2]), NonInstantGate(CNOT, 0.5))
+        _, t = apply(b[1], H, time=0.1)
+        uptotime(b[1], t + 0.25)
+        _, t = apply((b[1], b[2]), CNOT)
+        uptotime((b[1], b[2]), t + 0.5)
+        assert a.accesstimes == b.accesstimes and abs(a.accesstimes[0] - 0.85) < 1e-15
+        for obs in (tensor(Z, Z), tensor(X, X), tensor(Z, X), tensor(Y, Y)):
+            va, vb = env.values(observable(a[1:2], obs)), env.values(observable(b[1:2], obs))
+            assert np.allclose(va, vb, atol=1e-15), (bg, va, vb)
+        # and the closed form of the first step: H X1 = Z1 stays |0> under T1/T2 (no decay from the ground state)
+    reg = Register(1, env.repr("qo"), S.T2Dephasing(1.0))
+    initialize(reg[1])
+    apply(reg[1], NonInstantGate(H, 0.3))                          # |+> dephases for 0.3: <X> = exp(-0.3)
+    approx(env, observable(reg[1], X), np.exp(-0.3), atol=1e-15)
+
+
 ALL = [register_interface, apply_tensor_gate, cnot_bell_contracts, project_traceout_kats, unnormalized_state_error,
        observable_kats, permuted_graph_state, clifford_traceout, dense_traceout, entanglement_swap_chains,
-       purification_2to1, purification_3to1, depolarized_bell_pair, doctest_values]
+       purification_2to1, purification_3to1, depolarized_bell_pair, doctest_values, noninstant_gate]
