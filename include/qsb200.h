@@ -179,6 +179,24 @@ typedef struct qsb_program qsb_program;
 int qsb_record_begin(qsb_ctx* ctx);
 int qsb_record_end(qsb_ctx* ctx, qsb_program** out);
 int qsb_program_run(qsb_program* prog, uint64_t traj_shift, uint64_t draw_base);
+/* ---- cohort forking: outcome-dependent host control flow -----------------------------------
+ * The host follows ONE classical history per recorded program.  Where the reference branches on a measurement outcome
+ * and the branch changes what the host does next (`if !success ... end` after a purification,
+ * src/CircuitZoo/CircuitZoo.jl:156-160 and examples/firstgenrepeater_lowlevel/setup.jl:209-237), the host picks one
+ * branch for the program being recorded and calls qsb_ctx_retire with the lanes whose outcome disagrees: from that op on
+ * they count in no statistic of this program, and codes_dev[lane] (nullable; int32 per trajectory of the context, lane =
+ * index inside the context's ensemble) is set to `code`.  The host then records the program of the other history once
+ * (cached: the tree of programs depends on the schedule only) and re-runs the retired lanes under it from t = 0 with
+ * qsb_program_run_lanes / qsb_wave_run: lane i of a job is the trajectory with lane index lanes_dev[i] (same global id,
+ * same draws: its run is identical up to the fork and continues on its own branch).  Statistics rows and per-trajectory
+ * rows are indexed by lane index, so every program of the tree writes into the same buffers; flags & QSB_RUN_KEEP_STATS
+ * accumulates into the statistics rows instead of zeroing them first.  qsb_wave_run executes any number of (program,
+ * lane subset) jobs in ONE launch pair (tableau programs; lanes_dev[j] == NULL runs job j on the whole ensemble). */
+enum { QSB_RUN_KEEP_STATS = 1 };
+int qsb_ctx_retire(qsb_ctx* ctx, const qsb_mask* lanes, int32_t code, int32_t* codes_dev);
+int qsb_program_run_lanes(qsb_program* prog, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base, int flags);
+int qsb_wave_run(qsb_ctx* ctx, qsb_program* const* progs, const uint32_t* const* lanes_dev, const int64_t* counts, int njobs,
+                 uint64_t traj_shift, uint64_t draw_base, int flags);
 /* re-sends the recorded op list (the program's only host-side input) to the device, async on the stream */
 int qsb_program_upload(qsb_program* prog, int64_t* bytes);
 /* info: {ops, arena planes, statistics rows, threads per block, shared bytes per block, 1 if arena in global memory,

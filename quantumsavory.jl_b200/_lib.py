@@ -19,6 +19,7 @@ KET, DM, MCKET, TAB = 0, 1, 2, 3
 BASIS_X, BASIS_Y, BASIS_Z, BASIS_KETS = 1, 2, 3, 4
 OBS_PAULI, OBS_OP, OBS_PROJ_KET, OBS_PROJ_STAB = 0, 1, 2, 3
 MASK_AND, MASK_OR, MASK_XOR, MASK_ANDNOT, MASK_NOT, MASK_XNOR = range(6)
+RUN_KEEP_STATS = 1
 
 
 class QsbError(RuntimeError):
@@ -102,6 +103,9 @@ def _declare(L):
         "qsb_record_begin": (C.c_int, [vp]),
         "qsb_record_end": (C.c_int, [vp, vpp]),
         "qsb_program_run": (C.c_int, [vp, C.c_uint64, C.c_uint64]),
+        "qsb_program_run_lanes": (C.c_int, [vp, vp, C.c_int64, C.c_uint64, C.c_uint64, C.c_int]),
+        "qsb_wave_run": (C.c_int, [vp, vpp, vpp, i64p, C.c_int, C.c_uint64, C.c_uint64, C.c_int]),
+        "qsb_ctx_retire": (C.c_int, [vp, vp, C.c_int32, vp]),
         "qsb_program_info": (C.c_int, [vp, i64p]),
         "qsb_program_upload": (C.c_int, [vp, i64p]),
         "qsb_program_table_bytes": (C.c_int, [vp, C.POINTER(C.c_uint64)]),

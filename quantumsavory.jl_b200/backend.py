@@ -45,6 +45,7 @@ class BatchContext:
         self.device = device
         self._draw = 0
         self.recording = False
+        self.fork = None      # cohorts.Fork while a program of a cohort tree is being recorded (bool(mask) then forks)
 
     def next_draw(self) -> int:
         d = self._draw
@@ -105,6 +106,12 @@ class Program:
 
     def run(self, traj_shift: int = 0, draw_base: int = 0):
         check(self.ctx.L.qsb_program_run(self.p, traj_shift, draw_base))
+
+    def run_lanes(self, lanes_dev: int | None, count: int, traj_shift: int = 0, draw_base: int = 0, keep_stats: bool = False):
+        """Runs the program on a subset of the ensemble: lanes_dev = device pointer to `count` uint32 lane indices
+        (None: every lane).  keep_stats accumulates into the statistics rows instead of zeroing them."""
+        check(self.ctx.L.qsb_program_run_lanes(self.p, C.c_void_p(lanes_dev) if lanes_dev else None, int(count), traj_shift, draw_base,
+                                               _lib.RUN_KEEP_STATS if keep_stats else 0))
 
     def upload(self) -> int:
         """Re-sends the host op list to the device (async H2D); returns the bytes copied."""
@@ -192,9 +199,14 @@ class BatchMask:
         return bits.astype(bool)
 
     def __bool__(self):
-        if self.ctx.ntraj != 1:
-            raise TypeError("a BatchMask over more than one trajectory has no single truth value; pass it as mask=")
-        return bool(self.count())
+        """`if mask:` -- one trajectory: its bit.  While a cohort tree records a program (ctx.fork): the branch this
+        program's classical history takes; the lanes that disagree are retired to the program of the other branch."""
+        if self.ctx.ntraj == 1 and self.ctx.fork is None:
+            return bool(self.count())
+        if self.ctx.fork is not None:
+            return self.ctx.fork.decide(self)
+        raise TypeError("a BatchMask over more than one trajectory has no single truth value; pass it as mask= "
+                        "(or run the schedule under cohorts.CohortTree, where `if mask:` forks the ensemble)")
 
 
 class BatchOutcome:
@@ -474,6 +486,8 @@ class CudaBatchState:
         """-> BatchValue.  stats_dev: optional device pointer (double[4]) that receives the statistics
         without a host sync (sync=False), e.g. a torch tensor that is NCCL-all-reduced later."""
         ctx = self.ctx
+        if ctx.fork is not None and not ctx.fork.tally:
+            return BatchValue(ctx, np.zeros(4))     # prefix of a cohort program: the parent program tallied this observable
         k = len(indices)
         sign = 0
         keep = None

@@ -20,6 +20,12 @@ def _is2(meas):
     return meas == 2
 
 
+def _branches(m) -> bool:
+    """Can `if m:` be evaluated -- a plain bool, one trajectory, or an ensemble whose host loop forks (cohorts.CohortTree)?"""
+    ctx = getattr(m, "ctx", None)
+    return ctx is None or ctx.ntraj == 1 or getattr(ctx, "fork", None) is not None
+
+
 class EntanglementSwap:
     def __call__(self, localL, remoteL, localR, remoteR):
         apply((localL, localR), ops.CNOT)
@@ -62,8 +68,11 @@ class Purify2to1:
         measa = project_traceout(sacrificedL, basis)
         measb = project_traceout(sacrificedR, basis)
         success = measa == measb
-        failure = (not success) if isinstance(success, bool) else (measa != measb)
-        traceout(purifiedL, purifiedR, mask=failure)  # if !success traceout!(purifiedL, purifiedR)
+        if _branches(success):
+            if not success:                            # the reference's own control flow (CircuitZoo.jl:156-158)
+                traceout(purifiedL, purifiedR)
+        else:                                          # lockstep ensemble without forking: per-trajectory mask
+            traceout(purifiedL, purifiedR, mask=(measa != measb))
         return success
 
 

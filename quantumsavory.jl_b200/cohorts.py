@@ -1,0 +1,192 @@
+"""Cohort forking: outcome-dependent HOST control flow for a lockstep ensemble.
+
+The reference runs one event loop per trajectory, so host code may branch on a measurement outcome and do
+something different afterwards -- a failed purification frees the purified pair and the entangler later
+refills those slots (/root/reference/src/CircuitZoo/CircuitZoo.jl:156-160,
+examples/firstgenrepeater_lowlevel/setup.jl:209-237).  A batched backend sits under ONE host loop, which can follow
+one classical history at a time.  This module makes `if mask:` on a per-trajectory mask mean what it means in the
+reference:
+
+* the host schedule is recorded as a program (backend.BatchContext.record) under a *script* = the branches taken at
+  the first len(script) decisions; every later `if mask:` takes the default branch;
+* at each unscripted decision the lanes whose outcome disagrees are RETIRED from the program (qsb_ctx_retire): they
+  stop counting in its statistics and are marked with the ordinal of the decision;
+* the tree driver groups the retired lanes by (program, ordinal), records -- once, cached: the tree depends on the
+  schedule only, not on the trajectories -- the program whose script is the parent's decisions up to that ordinal
+  with the last one flipped, and re-runs those lanes under it FROM t = 0 with the same global trajectory ids (hence
+  the same draws: the re-run is bit-identical up to the fork, then continues on the lane's own branch).  Observables
+  before the fork are not tallied again (the parent counted them).  All cohorts of one tree level run as ONE fused
+  launch pair (qsb_wave_run).
+
+Every (trajectory, observable) is therefore counted exactly once, in the program whose classical history is that
+trajectory's own: the ensemble statistics and the per-trajectory series equal those of N independent runs of the
+reference's control flow (tests/test_gpu_cohorts.py compares every lane with an oracle twin that follows its own
+branches).  `max_depth` caps the number of forks per trajectory; a lane that disagrees once more is *censored*
+(dropped from later statistics, counted in `last["censored"]`) -- never silently continued on a wrong history.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+from . import _lib
+from ._lib import check
+
+CENSORED = 1 << 20   # added to the ordinal of a decision taken in a leaf program: the lane leaves the tree there
+
+
+class Fork:
+    """State of one recording of a cohort tree: which branch `if mask:` takes at each decision."""
+
+    def __init__(self, tree, script, leaf):
+        self.tree, self.script, self.leaf = tree, tuple(bool(b) for b in script), leaf
+        self.k = 0
+        self.taken = []
+
+    @property
+    def tally(self) -> bool:
+        """Observables before the last scripted decision were already counted by the parent program."""
+        return self.k >= len(self.script)
+
+    def decide(self, mask) -> bool:
+        cached = getattr(mask, "_decided", None)
+        if cached is not None:          # the same mask used in a second `if` (circuit, then protocol): same decision
+            return cached
+        k = self.k
+        self.k += 1
+        if k < len(self.script):
+            take = self.script[k]       # the lanes routed to this program agree with its script by construction
+        else:
+            take = self.tree.default
+            away = (~mask) if take else mask
+            ctx = mask.ctx
+            check(ctx.L.qsb_ctx_retire(ctx.p, away.p, k + (CENSORED if self.leaf else 0), C.c_void_p(self.tree.codes_ptr)))
+        mask._decided = take
+        self.taken.append(take)
+        return take
+
+
+class _Node:
+    __slots__ = ("script", "program", "taken", "children", "index")
+
+    def __init__(self, script, program, taken, index):
+        self.script, self.program, self.taken, self.children, self.index = script, program, tuple(taken), {}, index
+
+
+class CohortTree:
+    """schedule(): issues the host schedule once against `ctx` (called under ctx.record() with ctx.fork set).
+
+    run(traj_shift) executes the whole tree for one batch of ctx.ntraj trajectories; statistics rows must be zeroed by
+    the caller before (every program accumulates into the rows captured at record time)."""
+
+    def __init__(self, ctx, schedule, max_depth=None, default=True, max_programs=None):
+        import torch
+        self.torch = torch
+        self.ctx, self.schedule, self.max_depth, self.default, self.max_programs = ctx, schedule, max_depth, default, max_programs
+        self.device = torch.device("cuda", ctx.device)
+        self.codes = torch.full((ctx.ntraj,), -1, dtype=torch.int32, device=self.device)
+        self.codes_ptr = self.codes.data_ptr()
+        self.lane_node = torch.zeros(ctx.ntraj, dtype=torch.int32, device=self.device)
+        self.nodes = []
+        self.record_ms = 0.0
+        self.last = {}
+        self.root = self._record(())
+
+    # -- recording -----------------------------------------------------------------------------------
+    def _record(self, script):
+        import time
+        t0 = time.perf_counter()
+        ctx = self.ctx
+        leaf = self.max_depth is not None and sum(1 for i, b in enumerate(script) if b != self.default) >= self.max_depth
+        fork = Fork(self, script, leaf)
+        ctx.fork, ctx._draw = fork, 0
+        try:
+            with ctx.record() as rec:
+                self.schedule()
+        finally:
+            ctx.fork = None
+        node = _Node(tuple(script), rec.program, fork.taken, len(self.nodes))
+        self.nodes.append(node)
+        self.record_ms += 1e3 * (time.perf_counter() - t0)
+        return node
+
+    def child(self, node, ordinal):
+        """The program of the lanes that disagreed with `node` at decision `ordinal` (recorded on first use)."""
+        c = node.children.get(ordinal)
+        if c is None:
+            if self.max_programs is not None and len(self.nodes) >= self.max_programs:
+                return None
+            c = self._record(node.taken[:ordinal] + (not node.taken[ordinal],))
+            node.children[ordinal] = c
+        return c
+
+    # -- execution -----------------------------------------------------------------------------------
+    def _launch(self, jobs, traj_shift):
+        """jobs: list of (node, lanes device pointer or None, count) -> ONE fused launch pair."""
+        L, n = self.ctx.L, len(jobs)
+        progs = (C.c_void_p * n)(*[j[0].program.p.value for j in jobs])
+        lanes = (C.c_void_p * n)(*[j[1] for j in jobs])
+        counts = (C.c_int64 * n)(*[j[2] for j in jobs])
+        check(L.qsb_wave_run(self.ctx.p, progs, lanes, counts, n, traj_shift, 0, _lib.RUN_KEEP_STATS))
+
+    def run(self, traj_shift: int = 0):
+        torch = self.torch
+        ctx = self.ctx
+        tstream = torch.cuda.current_stream(self.device)   # the routing below runs on torch's stream, the launches on the context's:
+        self.codes.fill_(-1)                                # fence both ways unless the context was created on torch's stream
+        self.lane_node.zero_()
+        tstream.synchronize()
+        self._launch([(self.root, None, ctx.ntraj)], traj_shift)
+        levels, rerun, censored, new_programs, dropped = 1, 0, 0, 0, 0
+        jobs_per_level = [1]
+        nprog0 = len(self.nodes)
+        while True:
+            ctx.sync()
+            idx = torch.nonzero(self.codes >= 0).squeeze(1)          # lanes retired in the level that just ran
+            if idx.numel() == 0:                                       # (host sync: the tree is explored level by level)
+                break
+            c = self.codes[idx]
+            cens = c >= CENSORED
+            ncens = int(cens.sum())
+            censored += ncens
+            if ncens:
+                keep = ~cens
+                idx, c = idx[keep], c[keep]
+            self.codes.fill_(-1)
+            if idx.numel() == 0:
+                break
+            key = self.lane_node[idx].to(torch.int64) * CENSORED + c.to(torch.int64)
+            key, order = torch.sort(key)
+            lanes = idx[order].to(torch.int32).contiguous()            # lane indices grouped by (program, ordinal)
+            uniq, counts = torch.unique_consecutive(key, return_counts=True)
+            uniq_h, counts_h = uniq.cpu().tolist(), counts.cpu().tolist()
+            jobs, child_ids, off = [], [], 0
+            base = lanes.data_ptr()
+            for k, cnt in zip(uniq_h, counts_h):
+                parent, ordinal = self.nodes[k // CENSORED], k % CENSORED
+                child = self.child(parent, ordinal)
+                if child is None:                                      # program budget exhausted: these lanes are dropped, and counted
+                    dropped += cnt
+                    child_ids.append(-1)
+                else:
+                    jobs.append((child, base + 4 * off, cnt))
+                    child_ids.append(child.index)
+                    rerun += cnt
+                off += cnt
+            self.lane_node[lanes.to(torch.int64)] = torch.repeat_interleave(
+                torch.tensor(child_ids, dtype=torch.int32, device=self.device), counts)
+            if not jobs:
+                break
+            self._keep = lanes                                         # the launch reads this tensor: keep it alive until the next level
+            tstream.synchronize()
+            self._launch(jobs, traj_shift)
+            levels += 1
+            jobs_per_level.append(len(jobs))
+        new_programs = len(self.nodes) - nprog0
+        self.last = {"levels": levels, "lanes_rerun": rerun, "censored": censored, "dropped": dropped, "programs": len(self.nodes),
+                     "programs_recorded_this_run": new_programs, "jobs_per_level": jobs_per_level}
+        return self.last
+
+    def free(self):
+        for n in self.nodes:
+            n.program.free()
+        self.nodes = []

@@ -37,9 +37,7 @@ struct qsb_program {
     qsb_ctx* ctx;
     qsb_dprogram* dprog;   // non-null: a dense program (qsb_dexec.cu); the tableau fields below are unused except d_stats
     DrawSpec* d_specs; int nspecs, nslots, slot_stride;
-    int dyn;               // 1: k_tab_exec<1> with `threads` as its run-time block size
     uint8_t* d_aux; int naux, nfolded;   // constant tables of folded ops
-    uint32_t* bits;        // [nwords][slot_stride] decision words written by k_draw_bits, read by k_tab_exec
     ExecOp* d_ops; int nops;
     TabObsArgs* d_obs; int nobs;
     double** d_stats; int nstats;
@@ -160,17 +158,27 @@ __global__ void k_zero_stats(double* const* ptrs, int n) {
 // Draw pass: ONE THREAD PER TRAJECTORY evaluates every stochastic op's Philox draw and its decision; a warp
 // ballot packs the 32 decisions of a word, so the bit-sliced pass below never runs Philox (which a
 // thread-per-word kernel would have to loop over its 32 lanes for, at 1/32 of the parallelism).
-__global__ void __launch_bounds__(256) k_draw_bits(const DrawSpec* __restrict__ specs, int nspecs, uint32_t* __restrict__ bits,
-                                                   size_t W, int slot_stride, uint64_t seed, uint64_t traj0, uint64_t draw_base) {
-    __shared__ DrawSpec sspec[QSB_DRAW_CHUNK];
-    const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;   // local trajectory; W*32 is a multiple of 32
-    const bool on = t < W * 32;                                       // whole warps are on or off together
+// Like the executor it runs any number of (program, lane subset) jobs per launch: block b belongs to the job with the
+// largest block0_draw <= b, thread t of a job draws for the trajectory whose lane index is lanes[t] (identity when null).
+__global__ void __launch_bounds__(256) k_draw_bits(WaveArgs a) {
+    __shared__ __align__(16) DrawSpec sspec[QSB_DRAW_CHUNK];   // filled with 16-byte copies
+    __shared__ ExecJob sjob;
+    if (threadIdx.x == 0) {
+        int lo = 0, hi = a.njobs - 1;
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (a.jobs[mid].block0_draw <= blockIdx.x) lo = mid; else hi = mid - 1; }
+        sjob = a.jobs[lo];
+    }
+    __syncthreads();
+    const DrawSpec* const specs = reinterpret_cast<const DrawSpec*>(sjob.specs);
+    const int nspecs = sjob.nspecs, slot_stride = sjob.slot_stride;
+    const size_t t = (blockIdx.x - sjob.block0_draw) * (size_t)blockDim.x + threadIdx.x;   // trajectory of the job; words*32 is a multiple of 32
+    const bool on = t < (size_t)sjob.words * 32;                      // whole warps are on or off together
     const unsigned lane = threadIdx.x & 31u;
-    uint32_t* row = bits + (on ? (t >> 5) : 0) * (size_t)slot_stride; // this word's slots are contiguous: slot order = spec order
+    uint32_t* row = sjob.bits + (on ? (t >> 5) : 0) * (size_t)slot_stride; // this word's slots are contiguous: slot order = spec order
     // decision words wait in registers (lane l holds the l-th pending word) until 32 of them go out as one 128-byte store
     uint32_t mine = 0;
     unsigned fill = 0;
-    const uint64_t traj = traj0 + t;
+    const uint64_t traj = a.traj0 + ((sjob.lanes && t < sjob.count) ? (uint64_t)__ldg(sjob.lanes + t) : (uint64_t)t);
     uint32_t blk[4];
     uint64_t have = ~0ull;   // Philox block currently in registers (two draws per block)
     auto push = [&](uint32_t word) {
@@ -185,8 +193,8 @@ __global__ void __launch_bounds__(256) k_draw_bits(const DrawSpec* __restrict__ 
         __syncthreads();
         for (int i = 0; i < nc; ++i) {
             const DrawSpec& s = sspec[i];
-            const uint64_t id = s.draw + draw_base;
-            if ((id >> 1) != have) { have = id >> 1; qsb_philox_block(seed, traj, have, blk); }
+            const uint64_t id = s.draw + a.draw_base;
+            if ((id >> 1) != have) { have = id >> 1; qsb_philox_block(a.seed, traj, have, blk); }
             const uint64_t k = ((id & 1) ? (((uint64_t)blk[3] << 32) | blk[2]) : (((uint64_t)blk[1] << 32) | blk[0])) >> 11;   // u = k / 2^53
             if (s.type == TOP_NOISE) {
                 if (!__any_sync(0xffffffffu, k > s.thr_any)) { push(0u); push(0u); continue; }   // the common case: nobody errs
@@ -209,23 +217,49 @@ __global__ void __launch_bounds__(256) k_draw_bits(const DrawSpec* __restrict__ 
     if (on && lane < fill) row[lane] = mine;
 }
 
-// the per-block-size instantiations live in qsb_exec_inst.cu (one object per size, csrc/Makefile)
-#define QSB_EXEC_SIZES(X) X(32) X(64) X(96) X(128) X(256)
-#define X(T) cudaError_t qsb_exec_launch_##T(const ExecArgs&, unsigned, int, cudaStream_t);
-QSB_EXEC_SIZES(X) X(0) X(1)
-#undef X
-const int qsb_exec_block_sizes[] = {
-#define X(T) T,
-    QSB_EXEC_SIZES(X)
-#undef X
-    0};
-qsb_exec_launch_fn qsb_exec_launcher(int threads) {
-    switch (threads) {
-#define X(T) case T: return qsb_exec_launch_##T;
-        QSB_EXEC_SIZES(X) X(0) X(1)
-#undef X
-        default: return nullptr;
+// the two instantiations live in qsb_exec_inst.cu (one object each, csrc/Makefile)
+cudaError_t qsb_exec_launch_0(const WaveArgs&, unsigned, int, int, cudaStream_t);
+cudaError_t qsb_exec_launch_1(const WaveArgs&, unsigned, int, int, cudaStream_t);
+qsb_exec_launch_fn qsb_exec_launcher(int variant) { return variant ? qsb_exec_launch_1 : qsb_exec_launch_0; }
+
+// Launch shape of the shared-memory executor for a set of jobs (words[j] = 32-trajectory words of job j, `planes` = the
+// largest arena among them).  A block runs for (ops x latency of an op body) whatever its width, and the tile capacity of
+// an SM fixes how many words are resident, so a small tail wave costs as much as a full one (10^6 firstgenrepeater
+// trajectories on 96-thread blocks: 1.1 waves, 3.22 ms; 909 312 trajectories, exactly one wave: 1.67 ms).  Choose the
+// fewest waves, then the fewest blocks per SM, then the smallest block (32..256 threads, partial warps allowed) that
+// covers every job.  Returns 0 when not even a 32-thread tile fits (the arena then lives in global memory).
+static int qsb_exec_shape(const qsb_ctx* ctx, const uint32_t* words, int njobs, int planes, long* blocks_out) {
+    int dev_smem = 0, sm_smem = 0, sms = 0;
+    cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
+    cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    const size_t per_thread = (size_t)planes * sizeof(plane_t), fixed = 1024 + QSB_EXEC_CHUNK * sizeof(ExecOp) + sizeof(ExecJob);
+    if (per_thread * 32 > (size_t)dev_smem) return 0;
+    auto blocks_of = [&](int t) { long b = 0; for (int j = 0; j < njobs; ++j) b += ((long)words[j] + t - 1) / t; return b; };
+    const char* force_t = getenv("QSB_EXEC_THREADS");   // tuning aid: pin the block size
+    if (force_t && atoi(force_t) >= 32 && atoi(force_t) <= 256 && per_thread * atoi(force_t) <= (size_t)dev_smem) {
+        if (blocks_out) *blocks_out = blocks_of(atoi(force_t));
+        return atoi(force_t);
     }
+    const int force_b = getenv("QSB_EXEC_BLOCKS_PER_SM") ? atoi(getenv("QSB_EXEC_BLOCKS_PER_SM")) : 0;   // tuning aid
+    long total = 0; for (int j = 0; j < njobs; ++j) total += words[j];
+    for (long w = 1;; ++w) {
+        for (int b = 1; b <= 8; ++b) {
+            if (force_b && b != force_b) continue;
+            long tmax = ((long)sm_smem / b - (long)fixed) / (long)per_thread;
+            if (tmax > 256) tmax = 256;
+            if ((size_t)tmax * per_thread > (size_t)dev_smem) tmax = (long)(dev_smem / per_thread);
+            if (tmax < 32) continue;
+            const long cap = (long)sms * b * w;     // blocks the device holds in w waves at b blocks per SM
+            if (blocks_of((int)tmax) > cap) continue;
+            int lo = 32, hi = (int)tmax;             // blocks_of is non-increasing in t: smallest block that still fits
+            while (lo < hi) { const int mid = (lo + hi) / 2; if (blocks_of(mid) <= cap) hi = mid; else lo = mid + 1; }
+            if (blocks_out) *blocks_out = blocks_of(lo);
+            return lo;
+        }
+        if (w > total + 1) break;   // cannot happen: one word per block always fits eventually
+    }
+    return 32;
 }
 
 // Offline re-packing of one arena.  The online allocator had to number units while the schedule was still
@@ -464,58 +498,14 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     up((void**)&P->d_stats, R->stats_ptrs.data(), R->stats_ptrs.size() * sizeof(double*));
     up((void**)&P->d_specs, specs.data(), specs.size() * sizeof(DrawSpec));
     up((void**)&P->d_aux, aux.data(), aux.size());
-    if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->bits, (size_t)P->slot_stride * ctx->nwords * sizeof(uint32_t));
     if (rc == QSB_OK) { cudaError_t e = cudaStreamSynchronize(ctx->stream); if (e != cudaSuccess) rc = QSB_ERR_CUDA; }  // host vectors die below
-    // launch shape: the largest block whose [planes][threads] tile fits, preferring a single wave
-    int dev_smem = 0;
-    cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
-    const long groups = (long)ctx->nwords * (32 / QSB_LANES);   // one thread per lane group
-    // Block size: measured on B200 (tools/sweep_threads.sh) the executor is issue bound, not wave bound -- larger blocks
-    // amortise the per-chunk op staging and win slightly; take the largest block that leaves >= 2 blocks per SM.
-    int best_t = 0, best_rank = -1;
-    const char* force_t = getenv("QSB_EXEC_THREADS");   // tuning aid: pin the block size
-    for (int bi = 0; qsb_exec_block_sizes[bi]; ++bi) {
-        const int t = qsb_exec_block_sizes[bi];
-        if (force_t && atoi(force_t) != t) continue;
-        size_t smem = (size_t)P->planes * t * sizeof(plane_t);
-        if (smem > (size_t)dev_smem) continue;
-        int per_sm = (int)((size_t)(228 * 1024) / (smem + 1024 + QSB_EXEC_CHUNK * sizeof(ExecOp)));
-        int rank = (per_sm >= 2 ? 1000 : 0) + t;
-        if (rank > best_rank) { best_rank = rank; best_t = t; }
-    }
-    // Whole waves.  A block runs for (ops x latency of an op body) whatever its width, and the tile capacity of an SM fixes how many
-    // lane groups are resident, so a small tail wave costs as much as a full one (10^6 firstgenrepeater trajectories on 96-thread
-    // blocks: 1.1 waves, 3.22 ms; 909 312 trajectories, exactly one wave: 1.67 ms).  The run-time sized variant (k_tab_exec<1>, any
-    // block size up to 256, partial warps allowed) spreads the lane groups evenly over the fewest waves that fit.
-    P->dyn = 0;
-    if (force_t && !best_t && atoi(force_t) >= 32 && atoi(force_t) <= 256 && (size_t)P->planes * atoi(force_t) * sizeof(plane_t) <= (size_t)dev_smem) { best_t = atoi(force_t); P->dyn = 1; }
-    else if (best_t && !force_t && !getenv("QSB_EXEC_NODYN")) {
-        int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-        int sm_smem = 0; cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
-        const size_t per_thread = (size_t)P->planes * sizeof(plane_t), fixed = 1024 + QSB_EXEC_CHUNK * sizeof(ExecOp);
-        auto waves_of = [&](int t, int per_sm) { long blocks = (groups + t - 1) / t; return (blocks + (long)sms * per_sm - 1) / ((long)sms * per_sm); };
-        const int fixed_per_sm = std::max(1, (int)((size_t)sm_smem / (per_thread * best_t + fixed)));
-        long best_w = waves_of(best_t, fixed_per_sm);
-        int dyn_t = 0;
-        const int force_b = getenv("QSB_EXEC_BLOCKS_PER_SM") ? atoi(getenv("QSB_EXEC_BLOCKS_PER_SM")) : 0;   // tuning aid
-        for (long w = 1; w < best_w || (force_b && w <= best_w); ++w) {
-            for (int b = 1; b <= 8 && !dyn_t; ++b) {
-                if (force_b && b != force_b) continue;
-                long tmax = ((long)sm_smem / b - (long)fixed) / (long)per_thread;
-                if (tmax > 256) tmax = 256;
-                if ((size_t)tmax * per_thread > (size_t)dev_smem) tmax = dev_smem / per_thread;
-                long need = (groups + (long)sms * b * w - 1) / ((long)sms * b * w);
-                if (need < 32) need = 32;
-                if (need <= tmax && waves_of((int)need, b) <= w) dyn_t = (int)need;
-            }
-            if (dyn_t) break;
-        }
-        if (dyn_t) { best_t = dyn_t; P->dyn = 1; }
-    }
-    if (best_t) { P->threads = best_t; P->smem_bytes = P->planes * best_t * (int)sizeof(plane_t); P->arena = nullptr; }
+    // launch shape of the full-ensemble replay (reported by qsb_program_info; subsets and waves are shaped at run time)
+    const uint32_t full_words = (uint32_t)ctx->nwords;
+    const int t = qsb_exec_shape(ctx, &full_words, 1, P->planes, nullptr);
+    if (t) { P->threads = t; P->smem_bytes = P->planes * t * (int)sizeof(plane_t); P->arena = nullptr; }
     else {
         P->threads = 128; P->smem_bytes = 0;
-        if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->arena, (size_t)P->planes * groups * sizeof(plane_t));
+        if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->arena, (size_t)P->planes * ctx->nwords * sizeof(plane_t));
     }
     delete R;
     ctx->rec = nullptr;
@@ -524,48 +514,144 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     return QSB_OK;
 }
 
-// traj_shift moves the whole ensemble to fresh global trajectory ids (a new batch), draw_base offsets every draw id.
-extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t draw_base) {
-    if (!P) QSB_FAIL(QSB_ERR_BAD_ARG, "null program");
-    qsb_ctx* ctx = P->ctx;
+// ---------------------------------------------------------------------------------------------
+// run: one launch pair (draw pass + executor) over any number of (program, lane subset) jobs
+// ---------------------------------------------------------------------------------------------
+struct WaveJobIn { qsb_program* P; const uint32_t* lanes; int64_t count; };
+
+static int wave_buffer(qsb_ctx* ctx, void** buf, size_t* have, size_t need) {
+    if (*have >= need) return QSB_OK;
+    QSB_TRY(qsb_dev_free(ctx, *buf));   // stream ordered: launches already queued keep the old block until they finish
+    *buf = nullptr; *have = 0;
+    size_t want = need + need / 4;
+    QSB_TRY(qsb_dev_alloc(ctx, buf, want));
+    *have = want;
+    return QSB_OK;
+}
+
+static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shift, uint64_t draw_base, int flags) {
     if (ctx->rec) QSB_FAIL(QSB_ERR_BAD_ARG, "cannot run a program while recording");
     qsb_use_device(ctx);
-    if (P->nstats) {
-        QSB_PRE(ctx, "k_zero_stats");
-        k_zero_stats<<<(P->nstats + 127) / 128, 128, 0, ctx->stream>>>(P->d_stats, P->nstats);
-        QSB_LAUNCH_CHECK(ctx);
+    for (int j = 0; j < n; ++j) {
+        if (!in[j].P || in[j].P->ctx != ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "job %d: null program or program of another context", j);
+        if (in[j].count < 0 || in[j].count > ctx->ntraj) QSB_FAIL(QSB_ERR_BAD_ARG, "job %d: %lld lanes requested from an ensemble of %lld", j, (long long)in[j].count, (long long)ctx->ntraj);
+        if (in[j].P->dprog && (n > 1 || in[j].lanes || in[j].count != ctx->ntraj || (flags & QSB_RUN_KEEP_STATS)))
+            QSB_FAIL(QSB_ERR_UNSUPPORTED, "dense programs run on the whole ensemble, one program per launch");
+        if (in[j].P->arena && n > 1) QSB_FAIL(QSB_ERR_UNSUPPORTED, "a program whose arena lives in global memory cannot share a launch");
     }
-    if (P->dprog) {
+    if (!(flags & QSB_RUN_KEEP_STATS)) {
+        for (int j = 0; j < n; ++j) {
+            qsb_program* P = in[j].P;
+            if (!P->nstats) continue;
+            QSB_PRE(ctx, "k_zero_stats");
+            k_zero_stats<<<(P->nstats + 127) / 128, 128, 0, ctx->stream>>>(P->d_stats, P->nstats);
+            QSB_LAUNCH_CHECK(ctx);
+        }
+    }
+    if (n == 1 && in[0].P->dprog) {
+        qsb_program* P = in[0].P;
         QSB_TRY(qsb_dexec_run(P->dprog, traj_shift, draw_base));
         ctx->ops += P->ops_per_run; ctx->draws += P->draws_per_run;
         return QSB_OK;
     }
-    ExecArgs a;
-    a.ops = P->d_ops; a.nops = P->nops; a.obs = P->d_obs; a.aux = P->d_aux; a.arena = P->arena; a.valid = (const plane_t*)ctx->valid; a.W = (size_t)ctx->nwords * (32 / QSB_LANES);
+    std::vector<ExecJob> jobs(n);
+    std::vector<uint32_t> words(n);
+    size_t bits_words = 0;
+    int planes = 1, nspecs_any = 0;
+    for (int j = 0; j < n; ++j) {
+        qsb_program* P = in[j].P;
+        words[j] = (uint32_t)((in[j].count + 31) / 32);
+        bits_words += (size_t)words[j] * P->slot_stride;
+        planes = std::max(planes, P->planes);
+        nspecs_any |= P->nspecs;
+    }
+    QSB_TRY(wave_buffer(ctx, (void**)&ctx->wave_bits, &ctx->wave_bits_bytes, (bits_words + 32) * sizeof(uint32_t)));
+    QSB_TRY(wave_buffer(ctx, &ctx->wave_jobs, &ctx->wave_jobs_bytes, (size_t)n * sizeof(ExecJob)));
+    const bool global_arena = in[0].P->arena != nullptr;
+    long blocks = 0;
+    int threads;
+    if (global_arena) { threads = 128; blocks = (words[0] + 127) / 128; }
+    else if (n == 1 && !in[0].lanes && in[0].count == ctx->ntraj) { threads = in[0].P->threads; blocks = ((long)words[0] + threads - 1) / threads; }
+    else threads = qsb_exec_shape(ctx, words.data(), n, planes, &blocks);
+    if (!threads) QSB_FAIL(QSB_ERR_UNSUPPORTED, "a program of this launch does not fit in shared memory");
+    size_t boff = 0;
+    uint32_t be = 0, bd = 0;
+    for (int j = 0; j < n; ++j) {
+        qsb_program* P = in[j].P;
+        ExecJob& J = jobs[j];
+        J.ops = P->d_ops; J.obs = P->d_obs; J.aux = P->d_aux; J.specs = P->d_specs; J.lanes = in[j].lanes;
+        J.bits = ctx->wave_bits + boff; J.arena = (uint32_t*)P->arena;
+        J.nops = P->nops; J.nspecs = P->nspecs; J.slot_stride = P->slot_stride; J.planes = P->planes;
+        J.count = (uint32_t)in[j].count; J.words = words[j];
+        J.block0_exec = be; J.block0_draw = bd;
+        boff += (size_t)words[j] * P->slot_stride;
+        be += (words[j] + threads - 1) / threads;
+        bd += P->nspecs ? (uint32_t)(((size_t)words[j] * 32 + 255) / 256) : 0u;
+    }
+    // pageable source: the runtime stages the bytes before returning, so the host vector may die at once
+    QSB_CUDA(cudaMemcpyAsync(ctx->wave_jobs, jobs.data(), (size_t)n * sizeof(ExecJob), cudaMemcpyHostToDevice, ctx->stream));
+    WaveArgs a;
+    a.jobs = (const ExecJob*)ctx->wave_jobs; a.njobs = n;
     a.seed = ctx->seed; a.traj0 = (uint64_t)ctx->traj_offset + traj_shift; a.draw_base = draw_base;
-    a.bits = P->bits; a.slot_stride = P->slot_stride;
-    if (P->nspecs) {
+    if (bd) {
         QSB_PRE(ctx, "k_draw_bits");
-        k_draw_bits<<<(unsigned)((ctx->nwords * 32 + 255) / 256), 256, 0, ctx->stream>>>(P->d_specs, P->nspecs, P->bits, (size_t)ctx->nwords, P->slot_stride, a.seed, a.traj0, draw_base);
+        k_draw_bits<<<bd, 256, 0, ctx->stream>>>(a);
         QSB_LAUNCH_CHECK(ctx);
-        // decision words: written once by the draw pass, read once by the executor
-        qsb_account(ctx, "k_draw_bits", (uint64_t)P->nslots * ctx->nwords * 4 + (uint64_t)P->nspecs * sizeof(DrawSpec));
     }
-    unsigned blocks = (unsigned)((a.W + P->threads - 1) / P->threads);
-    QSB_PRE(ctx, "k_tab_exec");
-    {
-        qsb_exec_launch_fn launch = qsb_exec_launcher(P->arena ? 0 : (P->dyn ? 1 : P->threads));
-        a.dyn_threads = P->threads;
-        if (!launch) QSB_FAIL(QSB_ERR_BAD_ARG, "no executor compiled for %d threads per block", P->threads);
-        cudaError_t e = launch(a, blocks, P->smem_bytes, ctx->stream);
+    if (be) {
+        QSB_PRE(ctx, "k_tab_exec");
+        cudaError_t e = qsb_exec_launcher(global_arena ? 0 : 1)(a, be, threads, global_arena ? 0 : planes * threads * (int)sizeof(plane_t), ctx->stream);
         if (e != cudaSuccess) QSB_FAIL(QSB_ERR_CUDA, "k_tab_exec launch failed: %s", cudaGetErrorString(e));
+        QSB_LAUNCH_CHECK(ctx);
     }
-    QSB_LAUNCH_CHECK(ctx);
-    // compulsory HBM traffic of the fused launch: the op list and the valid words once, the statistics rows and
-    // any per-trajectory observable rows written once -- the ensemble state itself never leaves the SM
-    qsb_account(ctx, "k_tab_exec", (uint64_t)P->nops * sizeof(ExecOp) + (uint64_t)ctx->nwords * 4 + (uint64_t)P->nstats * 32 + (uint64_t)P->nslots * ctx->nwords * 4 +
-                                       P->per_traj_rows * (uint64_t)ctx->npad * 16);
-    ctx->ops += P->ops_per_run; ctx->draws += P->draws_per_run;
+    for (int j = 0; j < n; ++j) {
+        qsb_program* P = in[j].P;
+        const uint64_t nw = words[j], share_num = (uint64_t)in[j].count, share_den = (uint64_t)ctx->ntraj;
+        // decision words: written once by the draw pass, read once by the executor
+        if (P->nspecs) qsb_account(ctx, "k_draw_bits", (uint64_t)P->nslots * nw * 4 + (uint64_t)P->nspecs * sizeof(DrawSpec));
+        // compulsory HBM traffic of the fused launch: the op list once, the statistics rows and any per-trajectory observable
+        // rows written once, the decision words read once -- the ensemble state itself never leaves the SM
+        qsb_account(ctx, "k_tab_exec", (uint64_t)P->nops * sizeof(ExecOp) + (uint64_t)P->nstats * 32 + (uint64_t)P->nslots * nw * 4 +
+                                           P->per_traj_rows * (uint64_t)nw * 32 * 16);
+        ctx->ops += P->ops_per_run / share_den * share_num; ctx->draws += P->draws_per_run;
+    }
+    ctx->wave_threads = threads; ctx->wave_blocks = (int)be;
+    return QSB_OK;
+}
+
+// traj_shift moves the whole ensemble to fresh global trajectory ids (a new batch), draw_base offsets every draw id.
+extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t draw_base) {
+    if (!P) QSB_FAIL(QSB_ERR_BAD_ARG, "null program");
+    WaveJobIn in{P, nullptr, P->ctx->ntraj};
+    return run_wave(P->ctx, &in, 1, traj_shift, draw_base, 0);
+}
+
+extern "C" int qsb_program_run_lanes(qsb_program* P, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base, int flags) {
+    if (!P) QSB_FAIL(QSB_ERR_BAD_ARG, "null program");
+    WaveJobIn in{P, lanes_dev, lanes_dev ? count : P->ctx->ntraj};
+    return run_wave(P->ctx, &in, 1, traj_shift, draw_base, flags);
+}
+
+extern "C" int qsb_wave_run(qsb_ctx* ctx, qsb_program* const* progs, const uint32_t* const* lanes_dev, const int64_t* counts, int njobs,
+                            uint64_t traj_shift, uint64_t draw_base, int flags) {
+    if (!ctx || !progs || !counts || njobs < 1) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_wave_run: bad argument");
+    std::vector<WaveJobIn> in(njobs);
+    for (int j = 0; j < njobs; ++j) in[j] = WaveJobIn{progs[j], lanes_dev ? lanes_dev[j] : nullptr, (lanes_dev && lanes_dev[j]) ? counts[j] : ctx->ntraj};
+    return run_wave(ctx, in.data(), njobs, traj_shift, draw_base, flags);
+}
+
+// Cohort forking.  The lanes of `lanes` leave the lockstep ensemble at this point of the schedule: their
+// classical history differs from the one the host is following.  They stop counting in every later statistic of this run
+// and codes_dev[lane index] (nullable; int32 per trajectory of the context) receives `code`, so that the host can re-run
+// each retired lane under the program of its own history (qsb_wave_run with lane subsets).  Recorded programs only.
+extern "C" int qsb_ctx_retire(qsb_ctx* ctx, const qsb_mask* lanes, int32_t code, int32_t* codes_dev) {
+    if (!ctx || !lanes) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_ctx_retire: null argument");
+    if (!ctx->rec) QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_ctx_retire needs a recording: cohorts are re-run as recorded programs over lane subsets");
+    QSB_TRY(qsb_handle_ok(ctx, lanes->vplane >= 0, lanes->gen));
+    if (ctx->rec->dense) QSB_FAIL(QSB_ERR_UNSUPPORTED, "cohort forking of dense programs is not implemented");
+    QSB_TRY(qsb_rec_set_family(ctx, false));
+    TabOp* o = qsb_rec_push(ctx, TOP_RETIRE);
+    o->m[0] = lanes->vplane; o->u[0] = (uint32_t)code; o->per_traj = reinterpret_cast<double*>(codes_dev);
     return QSB_OK;
 }
 
@@ -574,6 +660,7 @@ extern "C" int qsb_program_run(qsb_program* P, uint64_t traj_shift, uint64_t dra
 extern "C" int qsb_program_upload(qsb_program* P, int64_t* bytes) {
     if (!P) QSB_FAIL(QSB_ERR_BAD_ARG, "null program");
     if (P->dprog) return qsb_dexec_upload(P->dprog, bytes);
+    qsb_use_device(P->ctx);
     size_t b = (size_t)P->nops * sizeof(ExecOp);
     if (b) QSB_CUDA(cudaMemcpyAsync(P->d_ops, P->h_ops, b, cudaMemcpyHostToDevice, P->ctx->stream));
     if (bytes) *bytes = (int64_t)b;
@@ -601,7 +688,7 @@ extern "C" int qsb_program_free(qsb_program* P) {
     qsb_ctx* ctx = P->ctx;
     if (P->dprog) { qsb_dexec_free(P->dprog); qsb_dev_free(ctx, P->d_stats); delete P; return QSB_OK; }
     qsb_dev_free(ctx, P->d_ops); qsb_dev_free(ctx, P->d_obs); qsb_dev_free(ctx, P->d_stats);
-    qsb_dev_free(ctx, P->d_specs); qsb_dev_free(ctx, P->bits); qsb_dev_free(ctx, P->d_aux);
+    qsb_dev_free(ctx, P->d_specs); qsb_dev_free(ctx, P->d_aux);
     if (P->arena) qsb_dev_free(ctx, P->arena);
     if (P->h_ops) cudaFreeHost(P->h_ops);
     delete P;

@@ -1,7 +1,7 @@
-// qsb_exec_inst.cu -- one instantiation of the fused executor kernel per compilation (-DQSB_EXEC_T=<threads>).
+// qsb_exec_inst.cu -- one instantiation of the fused executor kernel per compilation (-DQSB_EXEC_T=0|1).
 #include "qsb_exec_kernel.cuh"
 #ifndef QSB_EXEC_T
-#error "compile with -DQSB_EXEC_T=<threads per block> (0 = arena in global memory)"
+#error "compile with -DQSB_EXEC_T=1 (arena tile in shared memory) or 0 (arena in global memory)"
 #endif
 
 // The tableau functions are force-inlined with a LITERAL qubit count so that their loops unroll and their
@@ -10,30 +10,43 @@
 #define N_SWITCH(NV, ...) switch (NV) { N_CASE(1, __VA_ARGS__) N_CASE(2, __VA_ARGS__) N_CASE(3, __VA_ARGS__) N_CASE(4, __VA_ARGS__) \
                                         N_CASE(5, __VA_ARGS__) default: { const int N = (NV); __VA_ARGS__; } break; }
 
-// T > 0: the arena is a [planes][T] tile of shared memory (block of T threads, compile-time stride);
-// T == 0: the arena is in global memory with stride a.W (programs whose tile exceeds the shared memory of an SM).
-// T == 1: shared-memory tile whose stride is the RUN-TIME block size (any thread count up to 256, partial warps allowed), so the host
-// can size the blocks to cover the ensemble in whole waves (qsb_exec.cu: a 9 % tail wave used to double the run time).
+// T == 1: the arena is a [planes][blockDim.x] tile of shared memory.  The block size is a RUN-TIME value (any thread count
+//         up to 256, partial last warp allowed) so that the host can size the blocks to cover the ensemble in whole waves
+//         (qsb_exec.cu: a 9 % tail wave used to double the run time).
+// T == 0: the arena is in global memory with stride `words` (programs whose tile exceeds the shared memory of an SM).
+// One thread owns one 32-trajectory word column of every plane of its job; nothing is exchanged between threads, so
+// consecutive ops need no barrier.  `live` holds the lanes that still belong to the job's cohort (TOP_RETIRE).
 template <int T>
-__global__ void __launch_bounds__(T > 1 ? T : (T == 1 ? 256 : 128)) k_tab_exec(ExecArgs a) {
+__global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
     extern __shared__ plane_t tile[];
-    const size_t wg = blockIdx.x * (size_t)blockDim.x + threadIdx.x;  // global lane group (trajectories QSB_LANES*wg ..)
-    const bool on = wg < a.W;
-    plane_t* const base = T ? tile : a.arena;
-    const size_t W = T > 1 ? (size_t)T : (T == 1 ? (size_t)blockDim.x : a.W);
+    __shared__ ExecJob sjob;
+    __shared__ __align__(16) ExecOp sops[QSB_EXEC_CHUNK];   // filled with 16-byte copies
+    if (threadIdx.x == 0) {   // the job of this block: largest block0_exec <= blockIdx.x
+        int lo = 0, hi = a.njobs - 1;
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (a.jobs[mid].block0_exec <= blockIdx.x) lo = mid; else hi = mid - 1; }
+        sjob = a.jobs[lo];
+    }
+    __syncthreads();
+    const ExecOp* const ops = sjob.ops;
+    const int nops = sjob.nops;
+    const uint32_t* const lanes = sjob.lanes;
+    const size_t wg = (blockIdx.x - sjob.block0_exec) * (size_t)blockDim.x + threadIdx.x;   // word of the job (trajectories 32*wg ..)
+    const bool on = wg < sjob.words;
+    plane_t* const base = T ? tile : sjob.arena;
+    const size_t W = T ? (size_t)blockDim.x : (size_t)sjob.words;
     const size_t w = T ? (size_t)threadIdx.x : (on ? wg : 0);
-    const uint32_t validw = on ? a.valid[wg] : 0u;
+    const uint32_t left = on ? sjob.count - (uint32_t)wg * 32u : 0u;
+    const uint32_t validw = left >= 32u ? 0xffffffffu : ((1u << left) - 1u);
+    uint32_t live = validw;
 #define PL(idx) (base + (size_t)(idx) * W)
-    // decision bits of this thread's lanes: word-major rows, the lanes sit at bit `bshift` of each 32-bit word
-    const uint32_t* const brow = a.bits + (on ? wg / (32 / QSB_LANES) : 0) * (size_t)a.slot_stride;
-    const int bshift = (int)(wg % (32 / QSB_LANES)) * QSB_LANES;
-#define DBITS(slot) ((__ldg(brow + (slot)) >> bshift) & QSB_FULL)
-    __shared__ ExecOp sops[QSB_EXEC_CHUNK];
-    for (int i = 0; i < a.nops; ++i) {
+#define LANE_ID(l) (lanes ? __ldg(lanes + wg * 32 + (l)) : (uint32_t)(wg * 32 + (l)))
+    const uint32_t* const brow = sjob.bits + (on ? wg : 0) * (size_t)sjob.slot_stride;   // decision words of this thread's lanes
+#define DBITS(slot) (__ldg(brow + (slot)))
+    for (int i = 0; i < nops; ++i) {
         if ((i % QSB_EXEC_CHUNK) == 0) {   // refill: the whole block copies the next chunk of ops (coalesced 16-byte loads)
             __syncthreads();
-            const int nchunk = min(QSB_EXEC_CHUNK, a.nops - i);
-            const uint4* src = reinterpret_cast<const uint4*>(a.ops + i);
+            const int nchunk = min(QSB_EXEC_CHUNK, nops - i);
+            const uint4* src = reinterpret_cast<const uint4*>(ops + i);
             uint4* dst = reinterpret_cast<uint4*>(sops);
             for (int k = threadIdx.x; k < nchunk * (int)(sizeof(ExecOp) / 16); k += blockDim.x) dst[k] = __ldg(src + k);
             __syncthreads();
@@ -77,7 +90,7 @@ __global__ void __launch_bounds__(T > 1 ? T : (T == 1 ? 256 : 128)) k_tab_exec(E
                 uint32_t m[5];
                 const uint32_t b0 = DBITS(op.dslot), b1 = DBITS(op.dslot + 1), b2 = DBITS(op.dslot + 2);
                 for (int j = 0; j < 5; ++j) m[j] = ((j & 1) ? b0 : ~b0) & ((j & 2) ? b1 : ~b1) & ((j & 4) ? b2 : ~b2);
-                const uint8_t* tab = a.aux + op.obs;
+                const uint8_t* tab = sjob.aux + op.obs;
                 const int planes = op.n * (4 * op.n + 2);
                 for (int p = 0; p < planes; ++p) {
                     const uint32_t c = tab[p];
@@ -121,23 +134,23 @@ __global__ void __launch_bounds__(T > 1 ? T : (T == 1 ? 256 : 128)) k_tab_exec(E
             int n_alive = 0, num = 0, num2 = 0;
             int nelem = 1;
             if (on) {
-                const TabObsArgs& o = a.obs[op.obs];
+                const TabObsArgs& o = sjob.obs[op.obs];
                 nelem = o.nelem;
                 uint32_t cnt[8], cntm[8];
                 N_SWITCH(op.n, tab_expect_word_n(PL(op.s[0]), W, w, N, o, cnt, cntm))
-                const uint32_t al = PL(op.al[0])[w];
+                const uint32_t al = PL(op.al[0])[w] & live;   // retired lanes left this cohort: they are tallied where they continue
                 n_alive = __popc(al);
                 if (nelem == 1 && !op.per_traj) {   // a single Pauli: each lane holds -1, 0 or +1
                     num = __popc(cnt[0] & al) - __popc(cntm[0] & al);
                     num2 = __popc((cnt[0] | cntm[0]) & al);
                 } else {
                     const double inv = 1.0 / (double)nelem;
-                    for (int l = 0; l < QSB_LANES; ++l) {
+                    for (int l = 0; l < 32; ++l) {
                         int plus = 0, minus = 0;
                         for (int b = 0; b < 8; ++b) { plus |= ((cnt[b] >> l) & 1) << b; minus |= ((cntm[b] >> l) & 1) << b; }
                         const bool lane = (al >> l) & 1u;
                         const int d = lane ? plus - minus : 0;
-                        if (op.per_traj) { size_t t = wg * QSB_LANES + l; op.per_traj[2 * t] = (double)d * inv; op.per_traj[2 * t + 1] = 0.0; }
+                        if (op.per_traj && ((live >> l) & 1u)) { const size_t t = LANE_ID(l); op.per_traj[2 * t] = (double)d * inv; op.per_traj[2 * t + 1] = 0.0; }
                         num += d; num2 += d * d;
                     }
                 }
@@ -186,15 +199,27 @@ __global__ void __launch_bounds__(T > 1 ? T : (T == 1 ? 256 : 128)) k_tab_exec(E
         case TOP_ALIVE_COPY:
             if (on) PL(op.m[0])[w] = PL(op.al[0])[w];
             break;
+        case TOP_RETIRE:
+            // cohort forking: the lanes of the mask leave this cohort (their classical history differs from here on); each
+            // is marked with the op's code so that the host can route it to the program of its own history.  A retired lane
+            // keeps computing (its column is never read by anyone else) but no longer counts in any statistic.
+            if (on) {
+                const uint32_t r = (uint32_t)PL(op.m[0])[w] & live;
+                live &= ~r;
+                int32_t* const codes = reinterpret_cast<int32_t*>(op.per_traj);
+                if (codes) for (uint32_t t = r; t; t &= t - 1) codes[LANE_ID(__ffs((int)t) - 1)] = (int32_t)op.u[0];
+            }
+            break;
         }
     }
 #undef PL
 #undef DBITS
+#undef LANE_ID
 }
 
 #define QSB_CAT2(a, b) a##b
 #define QSB_CAT(a, b) QSB_CAT2(a, b)
-cudaError_t QSB_CAT(qsb_exec_launch_, QSB_EXEC_T)(const ExecArgs& a, unsigned blocks, int smem_bytes, cudaStream_t stream) {
+cudaError_t QSB_CAT(qsb_exec_launch_, QSB_EXEC_T)(const WaveArgs& a, unsigned blocks, int threads, int smem_bytes, cudaStream_t stream) {
     // the opt-in is per device (and per function): remember it for the device that is current for this launch
     static int configured[64];
     int dev = 0;
@@ -204,6 +229,6 @@ cudaError_t QSB_CAT(qsb_exec_launch_, QSB_EXEC_T)(const ExecArgs& a, unsigned bl
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) configured[dev] = smem_bytes;
     }
-    k_tab_exec<QSB_EXEC_T><<<blocks, QSB_EXEC_T > 1 ? QSB_EXEC_T : (QSB_EXEC_T == 1 ? a.dyn_threads : 128), smem_bytes, stream>>>(a);
+    k_tab_exec<QSB_EXEC_T><<<blocks, threads, smem_bytes, stream>>>(a);
     return cudaGetLastError();
 }

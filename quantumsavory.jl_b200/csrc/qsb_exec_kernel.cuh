@@ -1,11 +1,8 @@
 // qsb_exec_kernel.cuh -- the fused executor kernel of recorded tableau programs (see qsb_exec.cu).
-// Included by qsb_exec.cu (host side: ExecArgs) and by qsb_exec_inst.cu, which is compiled once per block
-// size T (-DQSB_EXEC_T=...) so that the instantiations build in parallel.
+// Included by qsb_exec.cu (host side: ExecJob / WaveArgs) and by qsb_exec_inst.cu, which is compiled once per
+// arena placement (-DQSB_EXEC_T=1 shared memory, 0 global memory) so that the instantiations build in parallel.
 #pragma once
-#ifndef QSB_EXEC_PLANE_T
-#define QSB_EXEC_PLANE_T uint32_t   // measured on B200: 32-lane words 5.21 ms, 16-lane 5.22 ms, 8-lane bytes 5.55 ms per 10^6 firstgenrepeater trajectories
-#endif
-#define QSB_PLANE_T QSB_EXEC_PLANE_T
+#define QSB_PLANE_T uint32_t    // measured on B200 (round 1): 32-lane words 5.21 ms, 16-lane 5.22 ms, 8-lane bytes 5.55 ms per 10^6 trajectories
 #define QSB_CORE_NS tabcorex
 #include "qsb_internal.cuh"
 #include "qsb_tab_core.cuh"
@@ -21,24 +18,29 @@ struct ExecOp {
     int16_t pad;
     int32_t obs, dslot;
     double* stats;
-    double* per_traj;
+    double* per_traj;         // TOP_EXPECT: per-trajectory row; TOP_RETIRE: int32 code row (one entry per lane of the context)
 };
 #define QSB_EXEC_CHUNK 32   // ops staged per shared-memory refill
 
-struct ExecArgs {
-    const ExecOp* ops; int nops;
+// One (program, lane subset) pair of a launch.  A launch ("wave") executes any number of jobs: block b belongs to the job
+// with the largest block0 <= b.  The full-ensemble replay is the one-job case with lanes == nullptr.
+struct ExecJob {
+    const ExecOp* ops;
     const TabObsArgs* obs;
     const uint8_t* aux;
-    plane_t* arena;           // nullptr -> shared-memory tile
-    const uint32_t* bits;     // decision words of every stochastic op, [word][slot_stride] (a word = 32 trajectories)
-    int slot_stride;
-    const plane_t* valid;
-    size_t W;                 // lane groups (threads) in the ensemble = trajectories / QSB_LANES
-    uint64_t seed, traj0, draw_base;
-    int dyn_threads;          // block size of the run-time sized variant (k_tab_exec<1>)
+    const void* specs;        // DrawSpec[nspecs] (qsb_exec.cu)
+    const uint32_t* lanes;    // lane index (trajectory slot of the context) of each of the job's `count` trajectories; nullptr: identity
+    uint32_t* bits;           // decision words of every stochastic op, [word][slot_stride] (a word = 32 trajectories of the job)
+    uint32_t* arena;          // global-memory arena [planes][words] (programs whose tile does not fit in shared memory), else nullptr
+    int nops, nspecs, slot_stride, planes;
+    uint32_t count, words;    // trajectories of the job, ceil(count / 32)
+    uint32_t block0_exec, block0_draw;   // first block of the job in the executor grid / in the draw grid
+};
+struct WaveArgs {
+    const ExecJob* jobs; int njobs;
+    uint64_t seed, traj0, draw_base;   // global trajectory id of lane index 0, offset of every draw id
 };
 
-// launchers, one per compiled block size (0 = arena in global memory)
-typedef cudaError_t (*qsb_exec_launch_fn)(const ExecArgs&, unsigned blocks, int smem_bytes, cudaStream_t stream);
-qsb_exec_launch_fn qsb_exec_launcher(int threads);   // nullptr when that block size is not compiled in
-extern const int qsb_exec_block_sizes[];             // 0-terminated list of the shared-memory block sizes
+// launchers: [0] arena in global memory (one job per launch), [1] shared-memory tile with a run-time block size
+typedef cudaError_t (*qsb_exec_launch_fn)(const WaveArgs&, unsigned blocks, int threads, int smem_bytes, cudaStream_t stream);
+qsb_exec_launch_fn qsb_exec_launcher(int variant);

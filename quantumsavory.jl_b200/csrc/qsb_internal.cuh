@@ -52,6 +52,10 @@ struct qsb_ctx {
     std::set<struct qsb_mask*>* live_masks;
     struct qsb_recorder* rec;  // non-null between qsb_record_begin and qsb_record_end
     int rec_gen;
+    // scratch of the fused launches (qsb_exec.cu), shared by every program of the context and grown on demand:
+    uint32_t* wave_bits; size_t wave_bits_bytes;   // decision words of the launch in flight (draw pass -> executor)
+    void* wave_jobs; size_t wave_jobs_bytes;       // job table of the launch in flight
+    int wave_threads, wave_blocks;                 // shape of the last executor launch (reported by tools)
 };
 
 struct qsb_state {
@@ -136,7 +140,7 @@ int qsbt_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* 
 // ---- recorded programs (qsb_exec.cu): tableau op lists executed by ONE fused launch ----------------
 enum { TOP_INIT, TOP_TENSOR, TOP_SELECT, TOP_COPY, TOP_GATE, TOP_NOISE, TOP_MEASURE, TOP_PTRACE, TOP_FORCE, TOP_EXPECT,
        TOP_MASK_FILL, TOP_MASK_LOGIC, TOP_MASK_RANDOM, TOP_KILL, TOP_ALIVE_COPY,
-       TOP_NOP, TOP_SELECT_CONST /* produced by constant folding at qsb_record_end */,
+       TOP_NOP, TOP_SELECT_CONST /* produced by constant folding at qsb_record_end */, TOP_RETIRE /* cohort forking */,
        // dense programs (qsb_dexec.cu): every state is held as a density matrix of 4^n elements in the element arena
        DOP_CONST, DOP_TENSOR, DOP_COPY, DOP_APPLY, DOP_CHANNEL, DOP_MEASURE, DOP_PTRACE, DOP_EXPECT };
 #define QSB_DEXEC_MAXN 5   /* largest state of a dense program: 4^5 elements per trajectory */

@@ -302,8 +302,8 @@ _OBSERVABLE_KW: dict = {}
 def observable_options(**kw):
     """Backend keywords (per_trajectory=True, ...) added to every observable() call inside the block, so a
     workload driver written against the reference's signature can be asked for per-trajectory values.
-    A callable value is called once per observable() that reaches the backend (e.g. stats_dev=next_row hands
-    every observable its own device statistics row)."""
+    A callable value is called once per observable() call, whether or not it reaches the backend (e.g. stats_dev=next_row
+    hands every sampling point its own device statistics row; the row of an unassigned slot stays zero)."""
     global _OBSERVABLE_KW
     old, _OBSERVABLE_KW = _OBSERVABLE_KW, {**_OBSERVABLE_KW, **kw}
     try:
@@ -316,6 +316,9 @@ def observable(refs, obs, something=None, time=None, **kw):
     """observable(refs, obs; something, time) -- src/baseops/observable.jl:12-41."""
     if _OBSERVABLE_KW:
         kw = {**_OBSERVABLE_KW, **kw}
+    # callables are evaluated for EVERY call, also one that ends at an unassigned slot below: a row handed out per call
+    # keeps its meaning (call index = sampling point) whatever the classical history of the run is
+    kw = {k: (v() if callable(v) else v) for k, v in kw.items()}
     regs, indices = _split(refs)
     if len(regs) != len(indices):
         raise ValueError("The number of registers does not match the number of slot indices.")
@@ -338,7 +341,6 @@ def observable(refs, obs, something=None, time=None, **kw):
     unique, offsets = unique_staterefs_with_offsets(staterefs)
     state = unique[0].state if len(unique) == 1 else unique[0].state.subsystemcompose(*[s.state for s in unique[1:]])
     state_indices = [r.stateindices[i - 1] + offsets[id(r.staterefs[i - 1])] for r, i in zip(regs, indices)]
-    kw = {k: (v() if callable(v) else v) for k, v in kw.items()}
     return state.observable(state_indices, obs, **kw)
 
 

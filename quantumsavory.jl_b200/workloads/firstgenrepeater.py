@@ -144,7 +144,8 @@ def purifier(net, nodea, nodeb, wait_time, busy_time):
         rega, regb = net.reg(nodea), net.reg(nodeb)
         circuit = Purify2to1(("X", "Z")[rnd % 2])
         success = circuit(rega[p1a], regb[p1b], rega[p2a], regb[p2b])
-        follow_success = bool(success) if isinstance(success, bool) or getattr(getattr(success, "ctx", None), "ntraj", 2) == 1 else True
+        from ..circuits import _branches
+        follow_success = bool(success) if _branches(success) else True     # masks mode: the ensemble shares the success branch
         if not follow_success:
             net.log["failures"] = net.log.get("failures", 0) + 1          # single-trajectory runs only (the twin of a lane)
             net.log.setdefault("first_failure_time", sim.now)

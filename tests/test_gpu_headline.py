@@ -74,25 +74,21 @@ def _compare_with_twins(formalism, follow, keys, per, nobs, ntraj, rtol=0.0):
     """per: [rows][2*npad] device tensor of the backend-reached observables, in call order (keys with flag True)."""
     import torch
     idx = torch.tensor(sorted(follow), device=per.device)
-    re = per[:nobs].view(nobs, -1, 2)[:, idx, 0].cpu().numpy()       # [row][followed lane]
-    rows = [i for i, k in enumerate(keys) if k[2]]
-    assert len(rows) == nobs
+    re = per[:nobs].view(nobs, -1, 2)[:, idx, 0].cpu().numpy()       # [row][followed lane]; row = index of the observable() call
+    assert len(keys) == nobs
     whole = 0
     for j, t in enumerate(sorted(follow)):
         orec, olog = _twin(formalism, t)
         t_fail = olog.get("first_failure_time", float("inf"))
         whole += t_fail == float("inf")
         assert [(k, tm) for k, tm, _ in orec] == [(k, tm) for k, tm, _ in keys]
-        r = 0
         checked = 0
         for i, (k, tm, reached) in enumerate(keys):
-            if reached:
-                if tm < t_fail:
-                    ov = orec[i][2].real
-                    gv = re[r, j]
-                    assert abs(gv - ov) <= rtol * max(1.0, abs(ov)), (formalism, t, k, tm, gv, ov)
-                    checked += 1
-                r += 1
+            if tm < t_fail:                  # an unassigned slot gives `something` = 0.0 on both sides (the row stays zero)
+                ov = orec[i][2].real
+                gv = re[i, j]
+                assert abs(gv - ov) <= rtol * max(1.0, abs(ov)), (formalism, t, k, tm, gv, ov)
+                checked += reached
         assert checked > 0
     return whole
 
@@ -118,7 +114,7 @@ def test_headline_clifford_program_at_the_benchmarked_shape(ntraj, force_threads
         assert info["threads"] == int(force_threads) and ((ntraj + 31) // 32) % info["threads"] != 0
     else:
         assert (ntraj + 31) // 32 > info["threads"] * 148 // 2          # more than one block per SM pair: a real multi-block grid
-    assert info["ops"] > 1000 and nobs == info["stats_rows"] > 200
+    assert info["ops"] > 1000 and nobs >= info["stats_rows"] > 200   # a sampling point before the first end-to-end pair reaches no state
     prog.run(); ctx.sync()
     rows_prog = s_prog.t[:nobs].clone()
     _, s_op, p_op, keys2, log2, nobs2 = _run_fgr(ctx, "clifford", "per_op", True)
@@ -148,7 +144,7 @@ def test_headline_dense_program_on_the_full_firstgenrepeater_dm_schedule():
     ctx = BatchContext(ntraj, seed=_bench().SEED)
     prog, s_prog, p_prog, keys, log, nobs = _run_fgr(ctx, "qo", "program", True)
     info = prog.info()
-    assert info["ops"] > 1000 and nobs == info["stats_rows"] > 200
+    assert info["ops"] > 1000 and nobs >= info["stats_rows"] > 200
     prog.run(); ctx.sync()
     _, s_op, p_op, keys2, log2, nobs2 = _run_fgr(ctx, "qo", "per_op", True)
     assert keys2 == keys and nobs2 == nobs and log2 == log
