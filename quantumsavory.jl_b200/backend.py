@@ -87,6 +87,16 @@ class BatchContext:
             self.L.qsb_ctx_destroy(self.p)
             self.p = None
 
+    def on_decision(self, mask, ordinal: int, take: bool, scripted: bool, fork):
+        """Called by cohorts.Fork when the host evaluates `if mask:` inside a recording.  The lanes routed to a program
+        agree with its script by construction; at an unscripted decision the lanes whose outcome disagrees with the
+        branch taken leave the program (qsb_ctx_retire), marked with the ordinal for the tree driver."""
+        if scripted:
+            return
+        from .cohorts import CENSORED
+        away = (~mask) if take else mask
+        check(self.L.qsb_ctx_retire(self.p, away.p, ordinal + (CENSORED if fork.leaf else 0), C.c_void_p(fork.tree.codes_ptr)))
+
     def mask(self, fill: bool) -> "BatchMask":
         p = C.c_void_p()
         check(self.L.qsb_mask_create(self.p, int(fill), C.byref(p)))

@@ -53,13 +53,9 @@ class Fork:
             return cached
         k = self.k
         self.k += 1
-        if k < len(self.script):
-            take = self.script[k]       # the lanes routed to this program agree with its script by construction
-        else:
-            take = self.tree.default
-            away = (~mask) if take else mask
-            ctx = mask.ctx
-            check(ctx.L.qsb_ctx_retire(ctx.p, away.p, k + (CENSORED if self.leaf else 0), C.c_void_p(self.tree.codes_ptr)))
+        scripted = k < len(self.script)
+        take = self.script[k] if scripted else self.tree.default
+        mask.ctx.on_decision(mask, k, take, scripted, self)   # the backend's part: retire the lanes that disagree
         mask._decided = take
         self.taken.append(take)
         return take
@@ -128,16 +124,22 @@ class CohortTree:
         counts = (C.c_int64 * n)(*[j[2] for j in jobs])
         check(L.qsb_wave_run(self.ctx.p, progs, lanes, counts, n, traj_shift, 0, _lib.RUN_KEEP_STATS))
 
-    def run(self, traj_shift: int = 0):
+    def run(self, traj_shift: int = 0, nlanes: int | None = None):
+        """One batch: every lane of the context (or the first `nlanes` lanes) through the tree of its own history."""
         torch = self.torch
         ctx = self.ctx
         tstream = torch.cuda.current_stream(self.device)   # the routing below runs on torch's stream, the launches on the context's:
         self.codes.fill_(-1)                                # fence both ways unless the context was created on torch's stream
         self.lane_node.zero_()
+        first = None
+        if nlanes is not None and nlanes < ctx.ntraj:
+            first = torch.arange(nlanes, dtype=torch.int32, device=self.device)
+        self._first = first                                   # read by the launch: keep it alive
         tstream.synchronize()
-        self._launch([(self.root, None, ctx.ntraj)], traj_shift)
+        self._launch([(self.root, first.data_ptr() if first is not None else None, nlanes if first is not None else ctx.ntraj)], traj_shift)
         levels, rerun, censored, new_programs, dropped = 1, 0, 0, 0, 0
-        jobs_per_level = [1]
+        jobs_per_level, lanes_per_level = [1], [nlanes if first is not None else ctx.ntraj]
+        h2d, d2h = 88, 0        # bytes that really cross PCIe/NVLink-C2C per batch: job tables down, cohort keys and sizes up
         nprog0 = len(self.nodes)
         while True:
             ctx.sync()
@@ -159,6 +161,7 @@ class CohortTree:
             lanes = idx[order].to(torch.int32).contiguous()            # lane indices grouped by (program, ordinal)
             uniq, counts = torch.unique_consecutive(key, return_counts=True)
             uniq_h, counts_h = uniq.cpu().tolist(), counts.cpu().tolist()
+            d2h += 16 * len(uniq_h) + 8
             jobs, child_ids, off = [], [], 0
             base = lanes.data_ptr()
             for k, cnt in zip(uniq_h, counts_h):
@@ -180,10 +183,12 @@ class CohortTree:
             tstream.synchronize()
             self._launch(jobs, traj_shift)
             levels += 1
-            jobs_per_level.append(len(jobs))
+            jobs_per_level.append(len(jobs)); lanes_per_level.append(sum(j[2] for j in jobs))
+            h2d += 88 * len(jobs)
         new_programs = len(self.nodes) - nprog0
         self.last = {"levels": levels, "lanes_rerun": rerun, "censored": censored, "dropped": dropped, "programs": len(self.nodes),
-                     "programs_recorded_this_run": new_programs, "jobs_per_level": jobs_per_level}
+                     "programs_recorded_this_run": new_programs, "jobs_per_level": jobs_per_level, "lanes_per_level": lanes_per_level,
+                     "h2d_bytes": h2d, "d2h_bytes": d2h}
         return self.last
 
     def free(self):
