@@ -197,6 +197,16 @@ int qsb_ctx_retire(qsb_ctx* ctx, const qsb_mask* lanes, int32_t code, int32_t* c
 int qsb_program_run_lanes(qsb_program* prog, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base, int flags);
 int qsb_wave_run(qsb_ctx* ctx, qsb_program* const* progs, const uint32_t* const* lanes_dev, const int64_t* counts, int njobs,
                  uint64_t traj_shift, uint64_t draw_base, int flags);
+/* Routing between two levels of the tree, on the device.  node_dev[lane] = index of the program the lane ran in last; a lane
+ * retired with code c < censor_base has key node * maxdec + c.  qsb_cohort_count returns the number of lanes per key
+ * (counts_host[nnodes * maxdec] = lanes retired with c >= censor_base: censored) -- the one host-visible step of a level;
+ * the host records the programs of new keys and calls qsb_cohort_scatter with, per key, the offset of its lanes in
+ * lanes_out_dev and the index of the program they continue in (-1: no program, the lanes are dropped): lanes_out_dev then
+ * holds the lane indices grouped by key (the lane subsets of the next qsb_wave_run), node_dev is updated and codes_dev is
+ * reset to -1. */
+int qsb_cohort_count(qsb_ctx* ctx, const int32_t* codes_dev, const int32_t* node_dev, int nnodes, int maxdec, int32_t censor_base, int32_t* counts_host);
+int qsb_cohort_scatter(qsb_ctx* ctx, int32_t* codes_dev, int32_t* node_dev, int nnodes, int maxdec, int32_t censor_base,
+                       const int32_t* offsets_host, const int32_t* child_host, uint32_t* lanes_out_dev);
 /* re-sends the recorded op list (the program's only host-side input) to the device, async on the stream */
 int qsb_program_upload(qsb_program* prog, int64_t* bytes);
 /* info: {ops, arena planes, statistics rows, threads per block, shared bytes per block, 1 if arena in global memory,

@@ -106,6 +106,8 @@ def _declare(L):
         "qsb_program_run_lanes": (C.c_int, [vp, vp, C.c_int64, C.c_uint64, C.c_uint64, C.c_int]),
         "qsb_wave_run": (C.c_int, [vp, vpp, vpp, i64p, C.c_int, C.c_uint64, C.c_uint64, C.c_int]),
         "qsb_ctx_retire": (C.c_int, [vp, vp, C.c_int32, vp]),
+        "qsb_cohort_count": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int32, vp]),
+        "qsb_cohort_scatter": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int32, vp, vp, vp]),
         "qsb_program_info": (C.c_int, [vp, i64p]),
         "qsb_program_upload": (C.c_int, [vp, i64p]),
         "qsb_program_table_bytes": (C.c_int, [vp, C.POINTER(C.c_uint64)]),

@@ -82,6 +82,8 @@ class CohortTree:
         self.codes = torch.full((ctx.ntraj,), -1, dtype=torch.int32, device=self.device)
         self.codes_ptr = self.codes.data_ptr()
         self.lane_node = torch.zeros(ctx.ntraj, dtype=torch.int32, device=self.device)
+        self.lanes_buf = [torch.zeros(ctx.ntraj, dtype=torch.int32, device=self.device) for _ in range(2)]   # lane subsets of the next level
+        self.maxdec = 1          # decisions per program seen so far (key = program * maxdec + ordinal)
         self.nodes = []
         self.record_ms = 0.0
         self.last = {}
@@ -102,6 +104,7 @@ class CohortTree:
             ctx.fork = None
         node = _Node(tuple(script), rec.program, fork.taken, len(self.nodes))
         self.nodes.append(node)
+        self.maxdec = max(self.maxdec, len(fork.taken))
         self.record_ms += 1e3 * (time.perf_counter() - t0)
         return node
 
@@ -125,11 +128,16 @@ class CohortTree:
         check(L.qsb_wave_run(self.ctx.p, progs, lanes, counts, n, traj_shift, 0, _lib.RUN_KEEP_STATS))
 
     def run(self, traj_shift: int = 0, nlanes: int | None = None):
-        """One batch: every lane of the context (or the first `nlanes` lanes) through the tree of its own history."""
+        """One batch: every lane of the context (or the first `nlanes` lanes) through the tree of its own history.
+
+        Per level: ONE fused launch pair over all cohorts (qsb_wave_run), then the routing of the retired lanes to the next
+        level on the device (qsb_cohort_count / qsb_cohort_scatter); the only host-visible step is the read-back of the
+        cohort sizes, because the host has to record the programs of histories it meets for the first time."""
+        import numpy as np
         torch = self.torch
-        ctx = self.ctx
-        tstream = torch.cuda.current_stream(self.device)   # the routing below runs on torch's stream, the launches on the context's:
-        self.codes.fill_(-1)                                # fence both ways unless the context was created on torch's stream
+        ctx, L = self.ctx, self.ctx.L
+        tstream = torch.cuda.current_stream(self.device)   # codes / lane tables are torch tensors used only as device buffers:
+        self.codes.fill_(-1)                                # fence once unless the context was created on torch's stream
         self.lane_node.zero_()
         first = None
         if nlanes is not None and nlanes < ctx.ntraj:
@@ -137,57 +145,44 @@ class CohortTree:
         self._first = first                                   # read by the launch: keep it alive
         tstream.synchronize()
         self._launch([(self.root, first.data_ptr() if first is not None else None, nlanes if first is not None else ctx.ntraj)], traj_shift)
-        levels, rerun, censored, new_programs, dropped = 1, 0, 0, 0, 0
+        levels, rerun, censored, dropped = 1, 0, 0, 0
         jobs_per_level, lanes_per_level = [1], [nlanes if first is not None else ctx.ntraj]
-        h2d, d2h = 88, 0        # bytes that really cross PCIe/NVLink-C2C per batch: job tables down, cohort keys and sizes up
+        h2d, d2h = 88, 0        # bytes that really cross PCIe/NVLink-C2C per batch: job tables and routing tables down, cohort sizes up
         nprog0 = len(self.nodes)
+        codes_p, node_p = C.c_void_p(self.codes_ptr), C.c_void_p(self.lane_node.data_ptr())
         while True:
-            ctx.sync()
-            idx = torch.nonzero(self.codes >= 0).squeeze(1)          # lanes retired in the level that just ran
-            if idx.numel() == 0:                                       # (host sync: the tree is explored level by level)
+            nn, md = len(self.nodes), self.maxdec
+            counts = np.zeros(nn * md + 1, np.int32)
+            check(L.qsb_cohort_count(ctx.p, codes_p, node_p, nn, md, CENSORED, counts.ctypes.data_as(C.c_void_p)))   # waits for the level
+            d2h += counts.nbytes
+            censored += int(counts[-1])
+            keys = np.flatnonzero(counts[:-1])
+            if keys.size == 0:
                 break
-            c = self.codes[idx]
-            cens = c >= CENSORED
-            ncens = int(cens.sum())
-            censored += ncens
-            if ncens:
-                keep = ~cens
-                idx, c = idx[keep], c[keep]
-            self.codes.fill_(-1)
-            if idx.numel() == 0:
-                break
-            key = self.lane_node[idx].to(torch.int64) * CENSORED + c.to(torch.int64)
-            key, order = torch.sort(key)
-            lanes = idx[order].to(torch.int32).contiguous()            # lane indices grouped by (program, ordinal)
-            uniq, counts = torch.unique_consecutive(key, return_counts=True)
-            uniq_h, counts_h = uniq.cpu().tolist(), counts.cpu().tolist()
-            d2h += 16 * len(uniq_h) + 8
-            jobs, child_ids, off = [], [], 0
-            base = lanes.data_ptr()
-            for k, cnt in zip(uniq_h, counts_h):
-                parent, ordinal = self.nodes[k // CENSORED], k % CENSORED
-                child = self.child(parent, ordinal)
-                if child is None:                                      # program budget exhausted: these lanes are dropped, and counted
+            offsets = np.zeros(nn * md, np.int32)
+            child = np.full(nn * md, -1, np.int32)
+            jobs, off = [], 0
+            base = self.lanes_buf[levels & 1].data_ptr()       # double buffered: the wave in flight reads the other half
+            for k in keys.tolist():
+                cnt = int(counts[k])
+                node = self.child(self.nodes[k // md], k % md)
+                if node is None:                               # program budget exhausted: these lanes are dropped, and counted
                     dropped += cnt
-                    child_ids.append(-1)
-                else:
-                    jobs.append((child, base + 4 * off, cnt))
-                    child_ids.append(child.index)
-                    rerun += cnt
+                    continue
+                offsets[k], child[k] = off, node.index
+                jobs.append((node, base + 4 * off, cnt))
                 off += cnt
-            self.lane_node[lanes.to(torch.int64)] = torch.repeat_interleave(
-                torch.tensor(child_ids, dtype=torch.int32, device=self.device), counts)
+            check(L.qsb_cohort_scatter(ctx.p, codes_p, node_p, nn, md, CENSORED, offsets.ctypes.data_as(C.c_void_p), child.ctypes.data_as(C.c_void_p), C.c_void_p(base)))
+            h2d += offsets.nbytes + child.nbytes
             if not jobs:
                 break
-            self._keep = lanes                                         # the launch reads this tensor: keep it alive until the next level
-            tstream.synchronize()
             self._launch(jobs, traj_shift)
+            rerun += off
             levels += 1
-            jobs_per_level.append(len(jobs)); lanes_per_level.append(sum(j[2] for j in jobs))
+            jobs_per_level.append(len(jobs)); lanes_per_level.append(off)
             h2d += 88 * len(jobs)
-        new_programs = len(self.nodes) - nprog0
         self.last = {"levels": levels, "lanes_rerun": rerun, "censored": censored, "dropped": dropped, "programs": len(self.nodes),
-                     "programs_recorded_this_run": new_programs, "jobs_per_level": jobs_per_level, "lanes_per_level": lanes_per_level,
+                     "programs_recorded_this_run": len(self.nodes) - nprog0, "jobs_per_level": jobs_per_level, "lanes_per_level": lanes_per_level,
                      "h2d_bytes": h2d, "d2h_bytes": d2h}
         return self.last
 

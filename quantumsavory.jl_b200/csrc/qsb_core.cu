@@ -309,6 +309,7 @@ extern "C" int qsb_ctx_destroy(qsb_ctx* ctx) {
     if (ctx->obs_buf) cudaFreeAsync(ctx->obs_buf, ctx->stream);
     if (ctx->wave_bits) cudaFreeAsync(ctx->wave_bits, ctx->stream);
     if (ctx->wave_jobs) cudaFreeAsync(ctx->wave_jobs, ctx->stream);
+    if (ctx->route_bins) cudaFreeAsync(ctx->route_bins, ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->prof) qsb_ctx_profile(ctx, 0);
     cudaMemPool_t pool;

@@ -696,3 +696,63 @@ extern "C" int qsb_program_free(qsb_program* P) {
 }
 
 void qsb_rec_note_stats(qsb_ctx* ctx, double* p) { if (p) ctx->rec->stats_ptrs.push_back(p); }
+
+// ---------------------------------------------------------------------------------------------
+// cohort routing: group the lanes a level retired by (program, decision) without leaving the device
+// ---------------------------------------------------------------------------------------------
+// key of a retired lane = node[lane] * maxdec + code[lane]; bins[key] counts them, bins[nkeys] counts the censored lanes
+__global__ void k_cohort_count(const int32_t* __restrict__ codes, const int32_t* __restrict__ node, int64_t ntraj, int maxdec, int32_t censor_base,
+                               int nkeys, int32_t* __restrict__ bins) {
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < ntraj; t += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t c = codes[t];
+        if (c < 0) continue;
+        if (c >= censor_base) { atomicAdd(&bins[nkeys], 1); continue; }
+        const int key = node[t] * maxdec + c;
+        if (key < nkeys) atomicAdd(&bins[key], 1);
+    }
+}
+// lanes_out[offset[key] + i] = the i-th lane of the key (order inside a cohort is arbitrary: lanes are independent and every
+// row a program writes is indexed by lane); node[lane] <- the program the lane continues in; codes reset for the next level
+__global__ void k_cohort_scatter(int32_t* __restrict__ codes, int32_t* __restrict__ node, int64_t ntraj, int maxdec, int32_t censor_base, int nkeys,
+                                 const int32_t* __restrict__ offset, const int32_t* __restrict__ child, int32_t* __restrict__ cursor, uint32_t* __restrict__ lanes_out) {
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < ntraj; t += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t c = codes[t];
+        if (c < 0) continue;
+        codes[t] = -1;
+        if (c >= censor_base) continue;
+        const int key = node[t] * maxdec + c;
+        if (key >= nkeys || child[key] < 0) continue;          // no program for this history (budget spent): the lane is dropped
+        lanes_out[offset[key] + atomicAdd(&cursor[key], 1)] = (uint32_t)t;
+        node[t] = child[key];
+    }
+}
+
+// counts_host[key] for key < nnodes * maxdec, counts_host[nnodes * maxdec] = censored lanes.  Host-visible (one D2H + sync per level).
+extern "C" int qsb_cohort_count(qsb_ctx* ctx, const int32_t* codes_dev, const int32_t* node_dev, int nnodes, int maxdec, int32_t censor_base, int32_t* counts_host) {
+    if (!ctx || !codes_dev || !node_dev || !counts_host || nnodes < 1 || maxdec < 1) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_cohort_count: bad argument");
+    const int nkeys = nnodes * maxdec;
+    QSB_TRY(wave_buffer(ctx, (void**)&ctx->route_bins, &ctx->route_bins_bytes, (size_t)(3 * nkeys + 4) * sizeof(int32_t)));
+    QSB_CUDA(cudaMemsetAsync(ctx->route_bins, 0, (size_t)(nkeys + 1) * sizeof(int32_t), ctx->stream));
+    QSB_PRE(ctx, "k_cohort_count");
+    k_cohort_count<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(codes_dev, node_dev, ctx->ntraj, maxdec, censor_base, nkeys, ctx->route_bins);
+    QSB_LAUNCH_CHECK(ctx);
+    QSB_CUDA(cudaMemcpyAsync(counts_host, ctx->route_bins, (size_t)(nkeys + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    QSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return QSB_OK;
+}
+// offsets_host / child_host: per key, where its lanes start in lanes_out_dev and which program they continue in (-1: dropped).
+// Must follow qsb_cohort_count with the same nnodes / maxdec (it reuses the device scratch).
+extern "C" int qsb_cohort_scatter(qsb_ctx* ctx, int32_t* codes_dev, int32_t* node_dev, int nnodes, int maxdec, int32_t censor_base,
+                                  const int32_t* offsets_host, const int32_t* child_host, uint32_t* lanes_out_dev) {
+    if (!ctx || !codes_dev || !node_dev || !offsets_host || !child_host || !lanes_out_dev) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_cohort_scatter: bad argument");
+    const int nkeys = nnodes * maxdec;
+    if (ctx->route_bins_bytes < (size_t)(3 * nkeys + 4) * sizeof(int32_t)) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_cohort_scatter without a matching qsb_cohort_count");
+    int32_t* off = ctx->route_bins + nkeys + 1; int32_t* ch = off + nkeys;
+    QSB_CUDA(cudaMemcpyAsync(off, offsets_host, (size_t)nkeys * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));   // pageable: staged before returning
+    QSB_CUDA(cudaMemcpyAsync(ch, child_host, (size_t)nkeys * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    QSB_CUDA(cudaMemsetAsync(ctx->route_bins, 0, (size_t)nkeys * sizeof(int32_t), ctx->stream));    // the bins become the per-key cursors
+    QSB_PRE(ctx, "k_cohort_scatter");
+    k_cohort_scatter<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(codes_dev, node_dev, ctx->ntraj, maxdec, censor_base, nkeys, off, ch, ctx->route_bins, lanes_out_dev);
+    QSB_LAUNCH_CHECK(ctx);
+    return QSB_OK;
+}

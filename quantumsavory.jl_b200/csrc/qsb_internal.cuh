@@ -56,6 +56,7 @@ struct qsb_ctx {
     uint32_t* wave_bits; size_t wave_bits_bytes;   // decision words of the launch in flight (draw pass -> executor)
     void* wave_jobs; size_t wave_jobs_bytes;       // job table of the launch in flight
     int wave_threads, wave_blocks;                 // shape of the last executor launch (reported by tools)
+    int32_t* route_bins; size_t route_bins_bytes;  // cohort routing scratch: counts / cursors, offsets, child programs per key
 };
 
 struct qsb_state {
