@@ -133,6 +133,18 @@ int qsb_apply_clifford(qsb_state* st, const int* idx, int k, const uint8_t* tabl
  * tables :106-173); KET: promoted to DM first (:1-4); MCKET: one sampled Kraus branch (:20-42);
  * TAB: Pauli noise, one draw always consumed (clifford/uptotime.jl:1-12,26-39; T1/T1T2 -> UNSUPPORTED). */
 int qsb_channel(qsb_state* st, int idx, int background, const double params[2], double dt, uint64_t draw_id);
+/* apply_noninstant!(state, state_indices, ConstantHamiltonianEvolution(H, duration), backgrounds) --
+ * src/backends/quantumoptics/noninstant.jl:10-37 (timeevolution.master / schroedinger / mcwf), and the
+ * `krausops === nothing` branch of uptotime! (uptotime.jl:24-29,51-54; H_ri == NULL, k == 1):
+ *   d rho/dt = -i[H, rho] + sum_j (L_j rho L_j' - 1/2 {L_j' L_j, rho}) for `duration`.
+ * H_ri: 2^k x 2^k Hamiltonian on idx[] (column-major, nullable = 0); L_ri: nl 2x2 collapse operators (lindbladop,
+ * noninstant.jl:44-97), operator j acting on subsystem idx[l_pos[j]].  The generator is constant, so the propagator
+ * exp(L t) of the k-qubit block is computed once on the host and applied in one pass (no solver tolerance).
+ * DM / KET (promoted with dm(), :21-23): exact.  MCKET: nl == 0 -> exp(-iHt) psi (:31-32); nl > 0 -> one sampled
+ * branch of the canonical Kraus form of exp(L t) (an unravelling whose ensemble mean is the master-equation solution,
+ * like mcwf :33-34; consumes draw_id; k == 1).  TAB: QSB_ERR_UNSUPPORTED (the reference has no method either). */
+int qsb_evolve(qsb_state* st, const int* idx, int k, const double* H_ri, int nl, const int* l_pos, const double* L_ri,
+               double duration, uint64_t draw_id);
 /* project_traceout!(state, stateindex, basis) -> (j, newstate): quantumoptics.jl:47-64 (+ express.jl:7-12
  * for symbolic X/Y/Z bases, mcket.jl:30-33) and clifford/express.jl:2-14.  The state shrinks in place
  * (nsub-1; 0 when the last subsystem was measured).  *outcome2 (new mask, caller frees) has bit t set

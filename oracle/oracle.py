@@ -50,6 +50,8 @@ def lib():
         L.qo_project_traceout.argtypes = [vp, C.c_int, dp, C.c_double, ip]
         L.qo_ptrace.argtypes = [vp, C.c_int]
         L.qo_expect_op.argtypes = [vp, ip, C.c_int, dp, dp]
+        L.qo_evolve_master.argtypes = [vp, ip, C.c_int, dp, C.c_int, ip, dp, C.c_double]
+        L.qo_evolve_mcwf.argtypes = [vp, ip, C.c_int, dp, C.c_int, ip, dp, C.c_double, C.c_uint64, C.c_uint64, C.c_uint64, ip]
         L.qo_expect_proj.argtypes = [vp, ip, C.c_int, dp, dp]
         L.qc_copy.argtypes = [vp]
         L.qc_free.argtypes = [vp]
@@ -177,6 +179,34 @@ class Dense:
         if rc:
             raise OracleError(rc)
         return br.value
+
+    @staticmethod
+    def _evo_args(idx, H, lind):
+        """lind: [(position in idx, 2x2 collapse operator)]"""
+        Hri = None if H is None else _ri(np.asarray(H, dtype=np.complex128).T.copy())
+        pos = np.array([p for p, _ in lind], dtype=np.int32)
+        Lri = _ri(np.stack([np.asarray(L, dtype=np.complex128).T.copy() for _, L in lind])) if lind else None
+        return (_ip(idx), len(idx), None if Hri is None else _dp(Hri), len(lind),
+                pos.ctypes.data_as(C.POINTER(C.c_int)) if lind else None, None if Lri is None else _dp(Lri)), (Hri, pos, Lri)
+
+    def evolve_master(self, idx, H, lind, duration):
+        """timeevolution.master on the embedded operators (adaptive DP5, reltol 1e-6 / abstol 1e-8)."""
+        args, keep = self._evo_args(idx, H, lind)
+        rc = lib().qo_evolve_master(self.p, *args, float(duration))
+        del keep
+        if rc:
+            raise OracleError(rc)
+        return self
+
+    def evolve_mcwf(self, idx, H, lind, duration, seed, traj, draw_id):
+        """timeevolution.schroedinger / mcwf on a trajectory ket; returns the number of jumps."""
+        args, keep = self._evo_args(idx, H, lind)
+        nj = C.c_int(0)
+        rc = lib().qo_evolve_mcwf(self.p, *args, float(duration), int(seed), int(traj), int(draw_id), C.byref(nj))
+        del keep
+        if rc:
+            raise OracleError(rc)
+        return nj.value
 
     def project_traceout(self, idx, psis, u):
         ps = np.stack([np.asarray(p, dtype=np.complex128) for p in psis])

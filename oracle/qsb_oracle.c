@@ -479,6 +479,194 @@ void qo_expect_proj(const qo_state* s, const int* idx, int k, const double* psi_
     free(psi);
 }
 
+/* ------------------------------------------------------------------------------------------
+ * Non-instant evolution: ConstantHamiltonianEvolution and the Lindblad fallback of uptotime!
+ *   src/noninstant.jl:21-35, src/backends/quantumoptics/noninstant.jl:1-37, uptotime.jl:24-29,51-54.
+ * The reference hands embedded operators to QuantumOptics' timeevolution.master / schroedinger / mcwf, which
+ * integrate with OrdinaryDiffEq's DP5 (Dormand-Prince 5(4), adaptive, reltol 1e-6 / abstol 1e-8 -- the package
+ * defaults; the packages are not vendored under /root/reference, so the published algorithm is restated):
+ *     master:        d rho/dt = -i (H rho - rho H) + sum_j (L_j rho L_j' - 1/2 L_j'L_j rho - 1/2 rho L_j'L_j)
+ *     schroedinger:  d psi/dt = -i H psi
+ *     mcwf:          d psi/dt = -i (H - i/2 sum L_j'L_j) psi until |psi|^2 drops to a uniform draw, then a jump
+ *                    psi <- L_j psi / |L_j psi| with probability ~ |L_j psi|^2, new draw, continue.
+ * Results carry the solver's tolerance: comparisons against the exact propagator use 1e-5.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct { int n; size_t D; const cplx* H; int nl; cplx* const* L; cplx* const* G; int is_dm; int nonherm; cplx* tmp; } evo_rhs;
+static void evo_f(const evo_rhs* e, const cplx* y, cplx* dy) {
+    size_t D = e->D;
+    if (e->is_dm) {
+        memset(dy, 0, D * D * sizeof(cplx));
+        if (e->H) {
+            matmul(D, e->H, y, e->tmp);
+            for (size_t i = 0; i < D * D; ++i) dy[i] += -I * e->tmp[i];
+            matmul(D, y, e->H, e->tmp);
+            for (size_t i = 0; i < D * D; ++i) dy[i] += I * e->tmp[i];
+        }
+        for (int j = 0; j < e->nl; ++j) {
+            cplx* t2 = e->tmp + D * D;
+            matmul(D, e->L[j], y, e->tmp); matmul_adj(D, e->tmp, e->L[j], t2);
+            for (size_t i = 0; i < D * D; ++i) dy[i] += t2[i];
+            matmul(D, e->G[j], y, e->tmp);
+            for (size_t i = 0; i < D * D; ++i) dy[i] -= 0.5 * e->tmp[i];
+            matmul(D, y, e->G[j], e->tmp);
+            for (size_t i = 0; i < D * D; ++i) dy[i] -= 0.5 * e->tmp[i];
+        }
+    } else {
+        for (size_t r = 0; r < D; ++r) {
+            cplx acc = 0;
+            if (e->H) for (size_t c = 0; c < D; ++c) acc += -I * e->H[r + c * D] * y[c];
+            if (e->nonherm) for (int j = 0; j < e->nl; ++j) for (size_t c = 0; c < D; ++c) acc += -0.5 * e->G[j][r + c * D] * y[c];
+            dy[r] = acc;
+        }
+    }
+}
+/* one Dormand-Prince step of size h from y (k1 = f(y) given); writes the 5th-order solution and returns the scaled
+ * error norm sqrt(mean(|err_i / (abstol + reltol max(|y_i|, |ynew_i|))|^2)) */
+static double dp5_step(const evo_rhs* e, size_t N, const cplx* y, const cplx* k1, double h, cplx* ynew, cplx* k7, cplx* work) {
+    static const double a21 = 1.0 / 5, a31 = 3.0 / 40, a32 = 9.0 / 40, a41 = 44.0 / 45, a42 = -56.0 / 15, a43 = 32.0 / 9,
+        a51 = 19372.0 / 6561, a52 = -25360.0 / 2187, a53 = 64448.0 / 6561, a54 = -212.0 / 729,
+        a61 = 9017.0 / 3168, a62 = -355.0 / 33, a63 = 46732.0 / 5247, a64 = 49.0 / 176, a65 = -5103.0 / 18656,
+        b1 = 35.0 / 384, b3 = 500.0 / 1113, b4 = 125.0 / 192, b5 = -2187.0 / 6784, b6 = 11.0 / 84,
+        e1 = 71.0 / 57600, e3 = -71.0 / 16695, e4 = 71.0 / 1920, e5 = -17253.0 / 339200, e6 = 22.0 / 525, e7 = -1.0 / 40;
+    cplx *k2 = work, *k3 = work + N, *k4 = work + 2 * N, *k5 = work + 3 * N, *k6 = work + 4 * N, *yt = work + 5 * N;
+    for (size_t i = 0; i < N; ++i) yt[i] = y[i] + h * a21 * k1[i];
+    evo_f(e, yt, k2);
+    for (size_t i = 0; i < N; ++i) yt[i] = y[i] + h * (a31 * k1[i] + a32 * k2[i]);
+    evo_f(e, yt, k3);
+    for (size_t i = 0; i < N; ++i) yt[i] = y[i] + h * (a41 * k1[i] + a42 * k2[i] + a43 * k3[i]);
+    evo_f(e, yt, k4);
+    for (size_t i = 0; i < N; ++i) yt[i] = y[i] + h * (a51 * k1[i] + a52 * k2[i] + a53 * k3[i] + a54 * k4[i]);
+    evo_f(e, yt, k5);
+    for (size_t i = 0; i < N; ++i) yt[i] = y[i] + h * (a61 * k1[i] + a62 * k2[i] + a63 * k3[i] + a64 * k4[i] + a65 * k5[i]);
+    evo_f(e, yt, k6);
+    for (size_t i = 0; i < N; ++i) ynew[i] = y[i] + h * (b1 * k1[i] + b3 * k3[i] + b4 * k4[i] + b5 * k5[i] + b6 * k6[i]);
+    evo_f(e, ynew, k7);
+    double acc = 0;
+    for (size_t i = 0; i < N; ++i) {
+        cplx err = h * (e1 * k1[i] + e3 * k3[i] + e4 * k4[i] + e5 * k5[i] + e6 * k6[i] + e7 * k7[i]);
+        double sc = 1e-8 + 1e-6 * fmax(cabs(y[i]), cabs(ynew[i]));
+        acc += (creal(err) * creal(err) + cimag(err) * cimag(err)) / (sc * sc);
+    }
+    return sqrt(acc / (double)N);
+}
+/* adaptive integration over [0, T]; stop_norm2 >= 0 (mcwf): return at the first accepted step after which |y|^2 <=
+ * stop_norm2, with *t_out the time reached.  Returns 0, or 4 when the step size underflows. */
+static int dp5_integrate(const evo_rhs* e, size_t N, cplx* y, double t0, double T, double stop_norm2, double* t_out) {
+    cplx* k1 = (cplx*)malloc(N * sizeof(cplx)); cplx* k7 = (cplx*)malloc(N * sizeof(cplx));
+    cplx* yn = (cplx*)malloc(N * sizeof(cplx)); cplx* work = (cplx*)malloc(6 * N * sizeof(cplx));
+    double t = t0, h = (T - t0) * 1e-2;
+    int rc = 0;
+    evo_f(e, y, k1);
+    while (t < T) {
+        if (t + h > T) h = T - t;
+        if (h < 1e-14 * fmax(1.0, fabs(T))) { rc = 4; break; }
+        double err = dp5_step(e, N, y, k1, h, yn, k7, work);
+        if (err <= 1.0) {
+            if (stop_norm2 >= 0) {
+                double n2 = 0; for (size_t i = 0; i < N; ++i) n2 += creal(yn[i]) * creal(yn[i]) + cimag(yn[i]) * cimag(yn[i]);
+                if (n2 <= stop_norm2) {
+                    /* the jump lies inside this step: bisect the step size on |y(t + s)|^2 = stop_norm2 (each trial is one more
+                     * DP5 step from the same start, the continuous-callback root search of the reference restated) */
+                    double lo = 0, hi = h;
+                    for (int it = 0; it < 40; ++it) {
+                        double mid = 0.5 * (lo + hi);
+                        dp5_step(e, N, y, k1, mid, yn, k7, work);
+                        double m2 = 0; for (size_t i = 0; i < N; ++i) m2 += creal(yn[i]) * creal(yn[i]) + cimag(yn[i]) * cimag(yn[i]);
+                        if (m2 <= stop_norm2) hi = mid; else lo = mid;
+                    }
+                    dp5_step(e, N, y, k1, hi, yn, k7, work);
+                    memcpy(y, yn, N * sizeof(cplx)); t += hi;
+                    break;
+                }
+            }
+            memcpy(y, yn, N * sizeof(cplx)); memcpy(k1, k7, N * sizeof(cplx));   /* first-same-as-last */
+            t += h;
+        }
+        double q = err > 0 ? 0.9 * pow(err, -0.2) : 5.0;
+        h *= fmin(5.0, fmax(0.2, q));
+    }
+    if (t_out) *t_out = t;
+    free(k1); free(k7); free(yn); free(work);
+    return rc;
+}
+/* builds the embedded operators exactly as _noninstant_operators / _embedded_lindblad_operators do (noninstant.jl:1-8,
+ * uptotime.jl:6-18): H = embed(basis, state_indices, H_k), L_j = embed(basis, [idx[l_pos[j]]], L_j) */
+static void evo_build(const qo_state* s, const int* idx, int k, const double* H_ri, int nl, const int* l_pos, const double* L_ri,
+                      cplx** H_out, cplx** L, cplx** G) {
+    size_t D = (size_t)1 << s->n, K = (size_t)1 << k;
+    *H_out = NULL;
+    if (H_ri) {
+        cplx* hk = (cplx*)malloc(K * K * sizeof(cplx));
+        for (size_t i = 0; i < K * K; ++i) hk[i] = H_ri[2 * i] + I * H_ri[2 * i + 1];
+        *H_out = (cplx*)malloc(D * D * sizeof(cplx));
+        qo_embed(s->n, idx, k, hk, *H_out);
+        free(hk);
+    }
+    for (int j = 0; j < nl; ++j) {
+        cplx l2[4];
+        for (int i = 0; i < 4; ++i) l2[i] = L_ri[8 * j + 2 * i] + I * L_ri[8 * j + 2 * i + 1];
+        L[j] = (cplx*)malloc(D * D * sizeof(cplx)); G[j] = (cplx*)malloc(D * D * sizeof(cplx));
+        int target = idx[l_pos[j]];
+        qo_embed(s->n, &target, 1, l2, L[j]);
+        for (size_t c = 0; c < D; ++c) for (size_t r = 0; r < D; ++r) { cplx acc = 0; for (size_t m = 0; m < D; ++m) acc += conj(L[j][m + r * D]) * L[j][m + c * D]; G[j][r + c * D] = acc; }
+    }
+}
+/* apply_noninstant!(state::Operator | Ket, ...) -> timeevolution.master (a Ket is promoted with dm(), noninstant.jl:21-23) */
+int qo_evolve_master(qo_state* s, const int* idx, int k, const double* H_ri, int nl, const int* l_pos, const double* L_ri, double duration) {
+    if (nl > 8) return 3;
+    if (s->kind == 0) { qo_state* p = qo_dm(s); free(s->d); s->d = p->d; s->kind = 1; free(p); }
+    size_t D = (size_t)1 << s->n;
+    cplx *H, *L[8], *G[8];
+    evo_build(s, idx, k, H_ri, nl, l_pos, L_ri, &H, L, G);
+    evo_rhs e = {s->n, D, H, nl, L, G, 1, 0, (cplx*)malloc(2 * D * D * sizeof(cplx))};
+    int rc = dp5_integrate(&e, D * D, s->d, 0.0, duration, -1.0, NULL);
+    free(e.tmp); free(H);
+    for (int j = 0; j < nl; ++j) { free(L[j]); free(G[j]); }
+    return rc;
+}
+/* apply_noninstant!(state::MCKet, ...): schroedinger when there are no collapse operators, else mcwf (noninstant.jl:25-37).
+ * Draws: u_j = qso_draw(seed, traj, draw_id + j * 2^32), j = 0, 1, ... (jump thresholds and jump choices alternate). */
+int qo_evolve_mcwf(qo_state* s, const int* idx, int k, const double* H_ri, int nl, const int* l_pos, const double* L_ri, double duration,
+                   uint64_t seed, uint64_t traj, uint64_t draw_id, int* njumps_out) {
+    if (s->kind != 0 || nl > 8) return 3;
+    size_t D = (size_t)1 << s->n;
+    cplx *H, *L[8], *G[8];
+    evo_build(s, idx, k, H_ri, nl, l_pos, L_ri, &H, L, G);
+    evo_rhs e = {s->n, D, H, nl, L, G, 0, 1, NULL};
+    int rc = 0, jumps = 0;
+    uint64_t sub = 0;
+    double t = 0;
+    if (nl == 0) rc = dp5_integrate(&e, D, s->d, 0.0, duration, -1.0, NULL);
+    else while (t < duration && rc == 0) {
+        double r = qso_draw(seed, traj, draw_id + ((sub++) << 32));
+        rc = dp5_integrate(&e, D, s->d, t, duration, r, &t);
+        if (rc || t >= duration) break;
+        double P[8] = {0}, total = 0;
+        cplx* br = (cplx*)malloc(D * sizeof(cplx));
+        for (int j = 0; j < nl; ++j) {
+            double nn = 0;
+            for (size_t r2 = 0; r2 < D; ++r2) { cplx acc = 0; for (size_t c = 0; c < D; ++c) acc += L[j][r2 + c * D] * s->d[c]; nn += creal(acc) * creal(acc) + cimag(acc) * cimag(acc); }
+            P[j] = nn; total += nn;
+        }
+        double thr = qso_draw(seed, traj, draw_id + ((sub++) << 32)) * total, cum = 0;
+        int sel = nl - 1;
+        for (int j = 0; j < nl; ++j) { cum += P[j]; if (cum > thr) { sel = j; break; } }
+        for (size_t r2 = 0; r2 < D; ++r2) { cplx acc = 0; for (size_t c = 0; c < D; ++c) acc += L[sel][r2 + c * D] * s->d[c]; br[r2] = acc; }
+        double nrm = sqrt(P[sel]);
+        for (size_t r2 = 0; r2 < D; ++r2) s->d[r2] = br[r2] / nrm;
+        free(br);
+        ++jumps;
+    }
+    double nn = 0;
+    for (size_t r2 = 0; r2 < D; ++r2) nn += creal(s->d[r2]) * creal(s->d[r2]) + cimag(s->d[r2]) * cimag(s->d[r2]);
+    nn = sqrt(nn);
+    for (size_t r2 = 0; r2 < D; ++r2) s->d[r2] /= nn;   /* mcwf returns normalised kets */
+    if (njumps_out) *njumps_out = jumps;
+    free(H);
+    for (int j = 0; j < nl; ++j) { free(L[j]); free(G[j]); }
+    return rc;
+}
+
 /* ==========================================================================================
  *                           STABILIZER (CliffordRepr) PART
  *  Generator-list representation of a (possibly mixed) stabilizer state: r <= n independent

@@ -90,6 +90,7 @@ def _declare(L):
         "qsb_apply": (C.c_int, [vp, ip, C.c_int, dp, vp]),
         "qsb_apply_clifford": (C.c_int, [vp, ip, C.c_int, u8p, vp]),
         "qsb_channel": (C.c_int, [vp, C.c_int, C.c_int, dp, C.c_double, C.c_uint64]),
+        "qsb_evolve": (C.c_int, [vp, ip, C.c_int, dp, C.c_int, ip, dp, C.c_double, C.c_uint64]),
         "qsb_measure": (C.c_int, [vp, C.c_int, C.c_int, dp, C.c_uint64, vpp, vpp, i64p]),
         "qsb_ptrace": (C.c_int, [vp, C.c_int, C.c_uint64]),
         "qsb_expect": (C.c_int, [vp, ip, C.c_int, C.c_int, vp, C.c_int, vp, vp, dp]),

@@ -467,7 +467,34 @@ class CudaBatchState:
             check(self.ctx.L.qsb_apply(self.p, _idx0(indices), len(indices), _dp(_colmajor_ri(mat)), m))
         return self
 
+    def _evolve(self, indices, H, lind, duration):
+        """lind: [(position in `indices`, 2x2 collapse operator)] -> qsb_evolve."""
+        k = len(indices)
+        Hri = None if H is None else _colmajor_ri(H)
+        pos = (C.c_int * max(1, len(lind)))(*[p for p, _ in lind])
+        Lri = np.concatenate([_colmajor_ri(L) for _, L in lind]) if lind else None
+        draw = self.ctx.next_draw() if (self.kind == MCKET and lind) else 0
+        check(self.ctx.L.qsb_evolve(self.p, _idx0(indices), k, None if Hri is None else _dp(Hri), len(lind),
+                                    pos if lind else None, None if Lri is None else _dp(Lri), float(duration), draw))
+        return self
+
+    def apply_noninstant(self, indices, operation, backgrounds):
+        """apply_noninstant!(state, state_indices, ConstantHamiltonianEvolution, backgrounds) --
+        src/backends/quantumoptics/noninstant.jl:1-37 (collapse operators: _embedded_lindblad_operators, uptotime.jl:6-18)."""
+        if self.kind == TAB:
+            raise _lib.MethodError(_lib.QSB_ERR_UNSUPPORTED, "apply_noninstant! has no method for a Clifford state")
+        H = operation.hamiltonian
+        H = H.mat if isinstance(H, ops.Gate) else np.asarray(H, dtype=np.complex128)
+        if H.shape[0] != 2 ** len(indices):
+            raise _lib.ArgumentError(_lib.QSB_ERR_BAD_ARG, "Hamiltonian size does not match the number of indices")
+        lind = [(j, L) for j, bg in enumerate(backgrounds) if bg is not None for L in S.lindbladop(bg)]
+        return self._evolve(indices, H, lind, operation.duration)
+
     def uptotime(self, idx, background, dt):
+        if isinstance(background, S.LindbladOnly):   # krausops === nothing: uptotime.jl:24-29 (mcwf), :51-54 (master)
+            if self.kind == TAB:
+                raise _lib.MethodError(_lib.QSB_ERR_UNSUPPORTED, "no Lindblad fallback for a Clifford state")
+            return self._evolve([idx], None, [(0, L) for L in S.lindbladop(background)], dt)
         prm = (C.c_double * 2)(*background.params)
         check(self.ctx.L.qsb_channel(self.p, int(idx) - 1, background.kind, prm, float(dt), self.ctx.next_draw()))
         return self

@@ -583,6 +583,15 @@ extern "C" int qsb_channel(qsb_state* st, int idx, int bg, const double params[2
     if (st->kind == QSB_TAB) return qsbt_channel(st, idx, bg, params, dt, draw_id);
     return qsbd_channel(st, idx, bg, params, dt, draw_id);
 }
+extern "C" int qsb_evolve(qsb_state* st, const int* idx, int k, const double* H_ri, int nl, const int* l_pos, const double* L_ri, double duration, uint64_t draw_id) {
+    QSB_TRY(check_idx(st, idx, k));
+    if (!qsb_is_dense(st->kind)) QSB_FAIL(QSB_ERR_UNSUPPORTED, "apply_noninstant! has no method for a tableau state");
+    if (k > 2) QSB_FAIL(QSB_ERR_UNSUPPORTED, "Hamiltonians on more than 2 subsystems are not implemented");
+    if (nl < 0 || nl > 8 || (nl > 0 && (!l_pos || !L_ri))) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_evolve: bad collapse operator list");
+    for (int j = 0; j < nl; ++j) if (l_pos[j] < 0 || l_pos[j] >= k) QSB_FAIL(QSB_ERR_BAD_INDEX, "qsb_evolve: collapse operator %d acts on entry %d of %d indices", j, l_pos[j], k);
+    if (!(duration >= 0)) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_evolve: negative duration");
+    return qsbd_evolve(st, idx, k, H_ri, nl, l_pos, L_ri, duration, draw_id);
+}
 extern "C" int qsb_measure(qsb_state* st, int idx, int basis, const double* kets, uint64_t draw_id,
                            qsb_mask** outcome2, qsb_mask** was_random, int64_t* counts_host) {
     QSB_TRY(check_idx(st, &idx, 1));

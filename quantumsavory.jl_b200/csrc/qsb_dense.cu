@@ -6,6 +6,7 @@
 // integer division is needed.  Every op is a single streaming pass: the roofline that bounds each
 // kernel is HBM bandwidth and its algorithmic bytes per trajectory are listed in DESIGN.md.
 #include <math.h>
+#include <stdlib.h>
 
 #include <vector>
 
@@ -370,6 +371,110 @@ __global__ void __launch_bounds__(TPB) k_apply_dm(double2* d, int64_t npad, size
     }
 }
 
+// ---- the same 4x4 conjugation with the 16 rows of a group staged through shared memory by the bulk-copy engine --------
+// (north_star: "large registers stream through TMA-staged tiles").  A block owns 128 consecutive trajectories, so element e
+// of a group is ONE contiguous 2 KB row d[e * npad + t0 .. t0 + 128): a stage is 16 rows = 32 KB moved by 16
+// cp.async.bulk copies that complete on an mbarrier; two stages, so the rows of group g + stride are in flight while group g
+// is computed; the results go back with cp.async.bulk shared -> global.  A thread only touches its own 16-byte column of
+// every row, so the update is in place in the stage and needs no barrier between load and compute.
+// Measured against the register path in profiles/ (tools/tma_experiment.py); selected with QSB_APPLY_TMA=1.
+#define TMA_ROWS 16
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count)); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile("{\n.reg .pred p;\nWAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+__global__ void __launch_bounds__(TPB) k_apply_dm2_tma(double2* d, int64_t npad, size_t groups, int n, GateArgs a) {
+    extern __shared__ __align__(128) unsigned char tma_smem[];
+    double2* const stage0 = reinterpret_cast<double2*>(tma_smem);
+#define STAGE(s) (stage0 + (s) * (TMA_ROWS * TPB))
+    __shared__ __align__(8) uint64_t full[2];
+    const size_t xtiles = (size_t)((npad + TPB - 1) / TPB);
+    // lanes 0..15 of warp 0 each own ONE row of the stage: lane i computes the address of row i = r + 4 c and issues its copy,
+    // so the 32 bulk copies of an item are not serialised behind one thread's address arithmetic
+    const int row = threadIdx.x & 15;
+    const bool issuer = threadIdx.x < TMA_ROWS;
+    size_t row_bits = 0;
+    {
+        const int r = row & 3, c = row >> 2;
+#pragma unroll
+        for (int b = 0; b < 2; ++b) row_bits |= ((size_t)((r >> b) & 1) << a.pos[b]) | ((size_t)((c >> b) & 1) << (a.pos[b] + n));
+    }
+    auto row_ptr = [&](size_t g, int64_t t0) {
+        size_t base = g;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) base = qsb_insert0(base, a.sorted[j]);
+        return d + (base | row_bits) * npad + t0;
+    };
+    auto bytes_of = [&](int64_t t0) { const int64_t left = npad - t0; return (uint32_t)((left < TPB ? left : TPB) * sizeof(double2)); };   // npad % 32 == 0: 16-byte granularity holds
+    if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    __syncthreads();
+    auto issue_load = [&](size_t g, int64_t t0, int s) {   // called by warp 0 (converged)
+        const uint32_t rb = bytes_of(t0);
+        if (threadIdx.x == 0) mbar_expect_tx(&full[s], rb * TMA_ROWS);
+        __syncwarp();
+        if (issuer) bulk_g2s(STAGE(s) + row * TPB, row_ptr(g, t0), rb, &full[s]);
+    };
+    // persistent 1-D grid: block b takes the (tile, group) items w = b, b + gridDim.x, ... with w = xt + xtiles * g
+    size_t g = blockIdx.x / xtiles;
+    int64_t xt = (int64_t)(blockIdx.x % xtiles);
+    const size_t dg = gridDim.x / xtiles; const int64_t dx = (int64_t)(gridDim.x % xtiles);   // the stride, split once
+    if (threadIdx.x < 32 && g < groups) issue_load(g, xt * TPB, 0);
+    uint32_t phases = 0;   // bit s = parity the next wait on full[s] expects
+    for (int s = 0; g < groups; s ^= 1) {
+        size_t gn = g + dg; int64_t xn = xt + dx;
+        if (xn >= (int64_t)xtiles) { xn -= xtiles; ++gn; }
+        if (threadIdx.x < 32 && gn < groups) {
+            // the other stage was stored by the previous trip: its shared-memory source must have been read before it is refilled
+            if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            issue_load(gn, xn * TPB, s ^ 1);
+        }
+        mbar_wait(&full[s], (phases >> s) & 1u);
+        phases ^= 1u << s;
+        const int64_t t0 = xt * TPB;
+        double2* col = STAGE(s) + threadIdx.x;
+        if ((int64_t)threadIdx.x < npad - t0) {
+            double2 x[4][4], y[4][4];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) x[i & 3][i >> 2] = col[i * TPB];
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    double2 acc = make_double2(0, 0);
+#pragma unroll
+                    for (int m = 0; m < 4; ++m) cfma(acc, a.u[r + m * 4], x[m][c]);
+                    y[r][c] = acc;
+                }
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    double2 acc = make_double2(0, 0);
+#pragma unroll
+                    for (int m = 0; m < 4; ++m) { double2 u = a.u[c + m * 4]; acc.x += y[r][m].x * u.x + y[r][m].y * u.y; acc.y += y[r][m].y * u.x - y[r][m].x * u.y; }
+                    col[(r + 4 * c) * TPB] = acc;
+                }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the bulk-copy engine
+        __syncthreads();
+        if (issuer) {
+            bulk_s2g(row_ptr(g, t0), STAGE(s) + row * TPB, bytes_of(t0));
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        g = gn; xt = xn;
+    }
+    if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+#undef STAGE
+}
+
 static void sort_ints(int* v, int n) { for (int i = 1; i < n; ++i) for (int j = i; j > 0 && v[j] < v[j - 1]; --j) { int s = v[j]; v[j] = v[j - 1]; v[j - 1] = s; } }
 
 int qsbd_apply(qsb_state* st, const int* idx, int k, const double* U, const qsb_mask* mask) {
@@ -402,7 +507,18 @@ int qsbd_apply(qsb_state* st, const int* idx, int k, const double* U, const qsb_
         size_t groups = (size_t)1 << (2 * n - 2 * k);
         Grid2 g = plan_grid(ctx, groups);
         QSB_PRE(ctx, "k_apply_dm");
+        const char* tma_env = getenv("QSB_APPLY_TMA");   // experiment switch, read per call so that a test can compare both paths
+        const int use_tma = tma_env ? atoi(tma_env) : 0;
         if (k == 1) k_apply_dm<1><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, n, a, mw);
+        else if (use_tma && !mw) {
+            const int smem = 2 * TMA_ROWS * TPB * (int)sizeof(double2);
+            static int configured[64];
+            if (ctx->device < 64 && !configured[ctx->device]) { QSB_CUDA(cudaFuncSetAttribute(k_apply_dm2_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); configured[ctx->device] = 1; }
+            // persistent 1-D grid: `use_tma` blocks of 64 KB per SM (2 measured best), every block walks its share of the (tile, group) items
+            size_t items = (size_t)((ctx->npad + TPB - 1) / TPB) * groups, nb = (size_t)ctx->sm_count * (use_tma > 3 ? 3 : use_tma);
+            if (nb > items) nb = items;
+            k_apply_dm2_tma<<<(unsigned)nb, TPB, smem, ctx->stream>>>((double2*)st->data, ctx->npad, groups, n, a);
+        }
         else k_apply_dm<2><<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, n, a, mw);
         qsb_account(ctx, "k_apply_dm", (uint64_t)32 * ((uint64_t)1 << (2 * n)) * ctx->ntraj);
     }
@@ -485,7 +601,6 @@ static int launch_rdm1(qsb_state* st, int q, int* nsplit_out) {
 }
 
 // ---- sampled Kraus branch on a trajectory ket (a6) ---------------------------------------------------
-struct KrausArgs { double2 k[4][4]; int nk; };
 __global__ void k_mc_finalize(const double* __restrict__ partial, int nsplit, int64_t npad, KrausArgs ka,
                               uint64_t seed, uint64_t traj0, uint64_t draw_id, double* __restrict__ scale, int* __restrict__ sel) {
     int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -561,26 +676,35 @@ static int host_kraus(int bg, const double* prm, double dt, KrausArgs* ka) {
     return QSB_OK;
 }
 
+// One sampled branch of a single-qubit Kraus set on a trajectory ket (uptotime.jl:20-42): probabilities from the reduced
+// 2x2 density matrix of the qubit, one draw, K_sel psi / |K_sel psi|.  Also the MCKet branch of qsb_evolve (qsb_evolve.cu).
+int qsbd_kraus_sampled(qsb_state* st, int idx, const KrausArgs& ka, uint64_t draw_id) {
+    qsb_ctx* ctx = st->ctx;
+    const int n = st->n;
+    if (ctx->rec) QSB_FAIL(QSB_ERR_UNSUPPORTED, "trajectory kets (QuantumMCRepr) cannot be recorded");
+    int nsplit;
+    QSB_TRY(launch_rdm1(st, idx, &nsplit));
+    double* scale = ctx->scratch + (size_t)nsplit * 4 * ctx->npad;
+    int* sel = (int*)(scale + ctx->npad);
+    QSB_PRE(ctx, "k_mc_finalize");
+    k_mc_finalize<<<(unsigned)((ctx->npad + 255) / 256), 256, 0, ctx->stream>>>(ctx->scratch, nsplit, ctx->npad, ka, ctx->seed, (uint64_t)ctx->traj_offset, draw_id, scale, sel);
+    QSB_LAUNCH_CHECK(ctx);
+    size_t groups = (size_t)1 << (n - 1);
+    Grid2 g = plan_grid(ctx, groups);
+    QSB_PRE(ctx, "k_apply_kraus_sel");
+    k_apply_kraus_sel<<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, idx, ka, scale, sel);
+    QSB_LAUNCH_CHECK(ctx);
+    qsb_account(ctx, "k_apply_kraus_sel", (uint64_t)32 * ((uint64_t)1 << n) * ctx->ntraj); ctx->ops += ctx->ntraj; ctx->draws++;
+    return QSB_OK;
+}
+
 int qsbd_channel(qsb_state* st, int idx, int bg, const double* prm, double dt, uint64_t draw_id) {
     qsb_ctx* ctx = st->ctx;
     int n = st->n;
     if (st->kind == QSB_MCKET) {
         KrausArgs ka;
         host_kraus(bg, prm, dt, &ka);
-        int nsplit;
-        QSB_TRY(launch_rdm1(st, idx, &nsplit));
-        double* scale = ctx->scratch + (size_t)nsplit * 4 * ctx->npad;
-        int* sel = (int*)(scale + ctx->npad);
-        QSB_PRE(ctx, "k_mc_finalize");
-        k_mc_finalize<<<(unsigned)((ctx->npad + 255) / 256), 256, 0, ctx->stream>>>(ctx->scratch, nsplit, ctx->npad, ka, ctx->seed, (uint64_t)ctx->traj_offset, draw_id, scale, sel);
-        QSB_LAUNCH_CHECK(ctx);
-        size_t groups = (size_t)1 << (n - 1);
-        Grid2 g = plan_grid(ctx, groups);
-        QSB_PRE(ctx, "k_apply_kraus_sel");
-        k_apply_kraus_sel<<<g.grid, TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, groups, idx, ka, scale, sel);
-        QSB_LAUNCH_CHECK(ctx);
-        qsb_account(ctx, "k_apply_kraus_sel", (uint64_t)32 * ((uint64_t)1 << n) * ctx->ntraj); ctx->ops += ctx->ntraj; ctx->draws++;
-        return QSB_OK;
+        return qsbd_kraus_sampled(st, idx, ka, draw_id);
     }
     if (st->kind == QSB_KET) QSB_TRY(qsbd_promote_dm(st));  // uptotime.jl:1-4
     ChanArgs p; memset(&p, 0, sizeof(p));

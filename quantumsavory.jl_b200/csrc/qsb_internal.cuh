@@ -120,6 +120,9 @@ int qsbd_to_host(const qsb_state* st, int64_t traj, double* out);
 int qsbd_tensor2(qsb_ctx* ctx, const qsb_state* a, const qsb_state* b, qsb_state** out);
 int qsbd_apply(qsb_state* st, const int* idx, int k, const double* U, const qsb_mask* mask);
 int qsbd_channel(qsb_state* st, int idx, int bg, const double* prm, double dt, uint64_t draw_id);
+struct KrausArgs { double2 k[4][4]; int nk; };   // up to four 2x2 Kraus operators, column-major k[m][r + 2c]
+int qsbd_kraus_sampled(qsb_state* st, int idx, const KrausArgs& ka, uint64_t draw_id);
+int qsbd_evolve(qsb_state* st, const int* idx, int k, const double* H_ri, int nl, const int* l_pos, const double* L_ri, double duration, uint64_t draw_id);
 int qsbd_measure(qsb_state* st, int idx, const double* kets, uint64_t draw_id, qsb_mask* outcome2, int64_t* counts_host);
 int qsbd_ptrace(qsb_state* st, int idx, uint64_t draw_id);
 int qsbd_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* obs, int obs_sign,

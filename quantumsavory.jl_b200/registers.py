@@ -12,6 +12,7 @@ driven without a Julia install):
     src/baseops/observable.jl         observable
     src/baseops/traceout.jl           traceout!, project_traceout!, removebackref!
     src/noninstant.jl:9-13            NonInstantGate
+    src/noninstant.jl:16-35           ConstantHamiltonianEvolution
 
 It is backend agnostic: any state object with the methods listed in backend.py works (the CUDA
 batched state in production, the oracle-backed single-trajectory state in tests), exactly like the
@@ -261,6 +262,16 @@ class NonInstantGate:
         self.gate, self.duration = gate, duration
 
 
+class ConstantHamiltonianEvolution:
+    """A Hamiltonian applied for `duration` -- src/noninstant.jl:16-19."""
+
+    def __init__(self, hamiltonian, duration):
+        self.hamiltonian, self.duration = hamiltonian, duration
+
+    def __repr__(self):
+        return f"ConstantHamiltonianEvolution(duration={self.duration})"
+
+
 def _normalize_mask(mask):
     """A mask over a single trajectory is a plain Bool (the reference's scalar control flow)."""
     if mask is None or isinstance(mask, bool):
@@ -285,6 +296,14 @@ def apply(refs, operation, time=None, mask=None):
                                f"simulation time is higher at t={max_time}. Consider using locks around the offending operations.")
         max_time = time
     uptotime(refs, max_time)
+    if isinstance(operation, ConstantHamiltonianEvolution):   # src/noninstant.jl:21-35
+        if mask is not None:
+            raise TypeError("ConstantHamiltonianEvolution takes no per-trajectory mask")
+        stateref = subsystemcompose(refs)
+        state_indices = [r.stateindices[i - 1] for r, i in zip(regs, indices)]
+        stateref.state = stateref.state.apply_noninstant(state_indices, operation, [r.backgrounds[i - 1] for r, i in zip(regs, indices)])
+        end_time = overwritetime(refs, max_time + operation.duration)
+        return refs, end_time
     if mask is False:  # single-trajectory condition not met: the time bookkeeping above still happens
         return refs, max_time
     stateref = subsystemcompose(refs)

@@ -151,6 +151,40 @@ class T1T2Noise:
         return (float(self.t1), float(self.t2))
 
 
+_LH = np.array([[0, 1], [0, 0]], dtype=C)  # sigmap = |0><1| (uptotime.jl:72)
+
+
+def lindbladop(bg):
+    """Collapse operators of a background -- src/backends/quantumoptics/noninstant.jl:44-97."""
+    if isinstance(bg, LindbladOnly):
+        return lindbladop(bg.noise)
+    if isinstance(bg, T1Decay):
+        return [_LH / math.sqrt(bg.t1)]                      # 1/sqrt(T1) |0><1|
+    if isinstance(bg, T2Dephasing):
+        return [Z / math.sqrt(2 * bg.t2)]                    # 1/sqrt(2 T2) Z
+    if isinstance(bg, T1T2Noise):
+        tphi_inv = 1 / bg.t2 - 1 / (2 * bg.t1)
+        if tphi_inv <= 0:                                    # no pure dephasing
+            return [_LH / math.sqrt(bg.t1)]
+        return [_LH / math.sqrt(bg.t1), Z / math.sqrt(2 / tphi_inv)]
+    if isinstance(bg, Depolarization):
+        raise RuntimeError("we do not have lindblad operators implemented for Depolarization")
+    raise TypeError(f"no lindbladop method for {bg!r}")
+
+
+@dataclasses.dataclass(frozen=True)
+class LindbladOnly:
+    """A background whose `krausops` is `nothing`: uptotime! falls back to the master equation / mcwf with
+    `lindbladop(noise)` (src/backends/quantumoptics/uptotime.jl:24-29,51-54 -- in the reference the qumode
+    AmplitudeDamping and PauliNoise take that route; this wrapper sends a qubit background down it)."""
+    noise: object
+    kind = -1
+
+    @property
+    def params(self):
+        return self.noise.params
+
+
 # ---- Clifford lowering ------------------------------------------------------------------------
 _PAULI_BITS = {(0, 0): Id, (1, 0): X, (0, 1): Z, (1, 1): Y}
 

@@ -352,6 +352,90 @@ def noninstant_gate(env):
     approx(env, observable(reg[1], X), np.exp(-0.3), atol=1e-15)
 
 
+def _second_moment(env, x):
+    """E[x^2] over the trajectories (env.values gives mean -/+ sigma for an ensemble, the value itself for one trajectory)."""
+    v = env.values(x)
+    return float(v[0]) ** 2 if len(v) == 1 else float(v[1]) ** 2 + ((float(v[2]) - float(v[0])) / 2) ** 2
+
+
+# noninstant_and_backgrounds_qubit_tests.jl:24-67: Kraus evolution == Lindblad evolution, composed == not composed -----
+def kraus_lindblad(env):
+    from qsb200.registers import ConstantHamiltonianEvolution
+    tol = getattr(env, "ode_atol", 1e-12)   # the oracle integrates with the reference's adaptive solver (reltol 1e-6)
+    singles = [(i, P) for i in (1, 2) for P in (X, Y, Z)]
+    pairs = [tensor(P, Q) for P in (X, Y, Z) for Q in (X, Y, Z)]
+
+    def same_single(ra, ia, rb, ib, atol):
+        for P in (X, Y, Z):
+            va, vb = env.values(observable(ra[ia], P)), env.values(observable(rb[ib], P))
+            assert np.allclose(va, vb, atol=atol), (P, va, vb)
+
+    def product_matches(reg, regb, atol):   # reg[1] (x) reg[2] vs the composed register
+        for i, P in singles:
+            assert np.allclose(env.values(observable(reg[i], P)), env.values(observable(regb[i], P)), atol=atol)
+        for k, PQ in enumerate(pairs):
+            P, Q = (X, Y, Z)[k // 3], (X, Y, Z)[k % 3]
+            prod = env.values(observable(reg[1], P))[len(env.values(observable(reg[1], P))) // 2] * \
+                env.values(observable(reg[2], Q))[len(env.values(observable(reg[2], Q))) // 2]
+            assert np.allclose(env.values(observable(regb[1:2], PQ)), prod, atol=atol), (k, prod)
+
+    for bg in (S.T1Decay(1.0), S.T2Dephasing(1.0), S.T1T2Noise(1.0, 1.0), S.T1T2Noise(1.0, 3.0)):
+        for init in (S.Z1, S.Z2, S.X1, S.X2):
+            reg = Register(2, env.repr("qo"), bg)
+            initialize(reg[1], init); initialize(reg[2], init)
+            uptotime(reg[1], 0.2)
+            uptotime(reg[2], 0.1); uptotime(reg[2], 0.2)
+            same_single(reg, 1, reg, 2, 1e-14)                       # Kraus weights compose
+            regb = Register(2, env.repr("qo"), bg)
+            initialize(regb[1], init); initialize(regb[2], init)
+            from qsb200.registers import subsystemcompose as compose
+            compose((regb[1], regb[2]))
+            uptotime(regb[1], 0.2)
+            uptotime(regb[2], 0.1); uptotime(regb[2], 0.2)
+            product_matches(reg, regb, 1e-14)
+            _, t_end = apply(reg[1], ConstantHamiltonianEvolution(ops.I, 0.1), time=0.3)   # Lindblad evolution
+            assert abs(t_end - 0.4) < 1e-15 and reg.accesstimes[0] == t_end                # overwritetime!, noninstant.jl:33
+            uptotime(reg[2], 0.4)                                                          # Kraus evolution
+            same_single(reg, 1, reg, 2, tol)
+            apply(regb[1], ConstantHamiltonianEvolution(ops.I, 0.1), time=0.3)
+            uptotime(regb[2], 0.4)
+            product_matches(reg, regb, tol)
+            # uptotime!'s own Lindblad route (krausops === nothing, uptotime.jl:51-54) against the Kraus closed form
+            regc = Register(1, env.repr("qo"), S.LindbladOnly(bg))
+            initialize(regc[1], init)
+            uptotime(regc[1], 0.2); uptotime(regc[1], 0.4)
+            same_single(regc, 1, reg, 2, tol)
+    with pytest.raises(RuntimeError, match="lindblad operators implemented for Depolarization"):
+        r = Register(1, env.repr("qo"), S.Depolarization(1.0))
+        initialize(r[1], S.X1)
+        apply(r[1], ConstantHamiltonianEvolution(ops.I, 0.1))
+
+
+# quantummc_repr_tests.jl:57-83: ConstantHamiltonianEvolution on trajectory kets (schroedinger / mcwf) --------------------
+def constant_hamiltonian_mc(env):
+    from qsb200.registers import ConstantHamiltonianEvolution
+    evolution = ConstantHamiltonianEvolution(np.pi / 2 * S.Z, 1.0)
+    reg = Register(1, env.repr("mc"))
+    initialize(reg[1], S.X1)
+    apply(reg[1], evolution)
+    approx(env, observable(reg[1], X), -1.0, atol=1e-6)                 # exp(-i pi/2 Z)|+> = -i|->
+    noisy = Register(1, env.repr("mc"), S.T2Dephasing(1.0))
+    initialize(noisy[1], S.X1)
+    apply(noisy[1], evolution)
+    assert abs(_second_moment(env, observable(noisy[1], X)) - 1.0) < 1e-6   # every trajectory stays pure: |<X>| = 1
+    comp = Register(2, env.repr("mc"), [S.T2Dephasing(1.0), None])
+    initialize(comp[1:2], ops.StabilizerState("XX ZZ"))
+    _, t = apply(comp[1], evolution)
+    assert t == 1.0 and stateof(comp[1]).state.nsubsystems == 2
+    assert abs(_second_moment(env, observable(comp[1:2], tensor(X, X))) - 1.0) < 1e-6   # Z-rotation by pi and Z jumps: XX -> +/- XX
+    # the same evolution on a density matrix: <X> = -exp(-1) (dephasing for one time unit at T2 = 1)
+    d = Register(1, env.repr("qo"), S.T2Dephasing(1.0))
+    initialize(d[1], S.X1)
+    apply(d[1], evolution)
+    approx(env, observable(d[1], X), -np.exp(-1.0), atol=max(getattr(env, "ode_atol", 1e-12), 1e-12))
+
+
 ALL = [register_interface, apply_tensor_gate, cnot_bell_contracts, project_traceout_kats, unnormalized_state_error,
        observable_kats, permuted_graph_state, clifford_traceout, dense_traceout, entanglement_swap_chains,
-       purification_2to1, purification_3to1, depolarized_bell_pair, doctest_values, noninstant_gate]
+       purification_2to1, purification_3to1, depolarized_bell_pair, doctest_values, noninstant_gate, kraus_lindblad,
+       constant_hamiltonian_mc]

@@ -112,7 +112,27 @@ class OracleState:
             self.s.apply(idx, op.mat if isinstance(op, ops.Gate) else np.asarray(op))
         return self
 
+    def _evolve(self, indices, H, lind, duration):
+        idx = [i - 1 for i in indices]
+        if self.flavor == "tab":
+            raise MethodError(3, "apply_noninstant! has no method for a Clifford state")
+        if self.is_mc:
+            d = self.ctx.next_draw() if lind else 0
+            self.s.evolve_mcwf(idx, H, lind, duration, self.ctx.seed, self.ctx.traj, d)
+        else:
+            self.s.evolve_master(idx, H, lind, duration)
+            self.flavor = "qo"
+        return self
+
+    def apply_noninstant(self, indices, operation, backgrounds):
+        H = operation.hamiltonian
+        H = H.mat if isinstance(H, ops.Gate) else np.asarray(H, dtype=np.complex128)
+        lind = [(j, L) for j, bg in enumerate(backgrounds) if bg is not None for L in S.lindbladop(bg)]
+        return self._evolve(indices, H, lind, operation.duration)
+
     def uptotime(self, idx, bg, dt):
+        if isinstance(bg, S.LindbladOnly):
+            return self._evolve([idx], None, [(0, L) for L in S.lindbladop(bg)], dt)
         d = self.ctx.next_draw()
         u = orc.draw(self.ctx.seed, self.ctx.traj, d)
         try:

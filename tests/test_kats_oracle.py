@@ -10,6 +10,7 @@ from tests.oracle_backend import OracleContext, OracleRepr
 
 class OracleEnv:
     ntraj = 1
+    ode_atol = 1e-6   # the oracle restates the reference's adaptive DP5 (reltol 1e-6, abstol 1e-8)
 
     def __init__(self, seed, traj):
         self.ctx = OracleContext(seed, traj)
