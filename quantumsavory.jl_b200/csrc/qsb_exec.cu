@@ -233,7 +233,7 @@ static int qsb_exec_shape(const qsb_ctx* ctx, const uint32_t* words, int njobs, 
     cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
     cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-    const size_t per_thread = (size_t)planes * sizeof(plane_t), fixed = 1024 + QSB_EXEC_CHUNK * sizeof(ExecOp) + sizeof(ExecJob);
+    const size_t per_thread = (size_t)qsb_exec_stride(planes) * sizeof(plane_t), fixed = 1024 + QSB_EXEC_CHUNK * sizeof(ExecOp) + sizeof(ExecJob);
     if (per_thread * 32 > (size_t)dev_smem) return 0;
     auto blocks_of = [&](int t) { long b = 0; for (int j = 0; j < njobs; ++j) b += ((long)words[j] + t - 1) / t; return b; };
     const char* force_t = getenv("QSB_EXEC_THREADS");   // tuning aid: pin the block size
@@ -502,7 +502,7 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     // launch shape of the full-ensemble replay (reported by qsb_program_info; subsets and waves are shaped at run time)
     const uint32_t full_words = (uint32_t)ctx->nwords;
     const int t = qsb_exec_shape(ctx, &full_words, 1, P->planes, nullptr);
-    if (t) { P->threads = t; P->smem_bytes = P->planes * t * (int)sizeof(plane_t); P->arena = nullptr; }
+    if (t) { P->threads = t; P->smem_bytes = qsb_exec_stride(P->planes) * t * (int)sizeof(plane_t); P->arena = nullptr; }
     else {
         P->threads = 128; P->smem_bytes = 0;
         if (rc == QSB_OK) rc = qsb_dev_alloc(ctx, (void**)&P->arena, (size_t)P->planes * ctx->nwords * sizeof(plane_t));
@@ -593,6 +593,7 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
     WaveArgs a;
     a.jobs = (const ExecJob*)ctx->wave_jobs; a.njobs = n;
     a.seed = ctx->seed; a.traj0 = (uint64_t)ctx->traj_offset + traj_shift; a.draw_base = draw_base;
+    a.tile_stride = qsb_exec_stride(planes);
     if (bd) {
         QSB_PRE(ctx, "k_draw_bits");
         k_draw_bits<<<bd, 256, 0, ctx->stream>>>(a);
@@ -600,7 +601,7 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
     }
     if (be) {
         QSB_PRE(ctx, "k_tab_exec");
-        cudaError_t e = qsb_exec_launcher(global_arena ? 0 : 1)(a, be, threads, global_arena ? 0 : planes * threads * (int)sizeof(plane_t), ctx->stream);
+        cudaError_t e = qsb_exec_launcher(global_arena ? 0 : 1)(a, be, threads, global_arena ? 0 : qsb_exec_stride(planes) * threads * (int)sizeof(plane_t), ctx->stream);
         if (e != cudaSuccess) QSB_FAIL(QSB_ERR_CUDA, "k_tab_exec launch failed: %s", cudaGetErrorString(e));
         QSB_LAUNCH_CHECK(ctx);
     }

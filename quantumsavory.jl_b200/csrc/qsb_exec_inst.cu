@@ -6,11 +6,21 @@
 
 // The tableau functions are force-inlined with a LITERAL qubit count so that their loops unroll and their
 // per-row scratch arrays live in registers (a run-time n keeps them in local memory: 2.2 KB of stack per thread).
+// States of more than 5 qubits take a NOINLINE fallback with a run-time n (its arrays live in local memory); keeping it out of
+// line lets the compiler allocate registers for the literal cases alone (inline it cost 2.2 KB of stack frame and capped the
+// kernel at 64 registers with spills).
 #define N_CASE(K, ...) case K: { constexpr int N = K; __VA_ARGS__; } break;
-#define N_SWITCH(NV, ...) switch (NV) { N_CASE(1, __VA_ARGS__) N_CASE(2, __VA_ARGS__) N_CASE(3, __VA_ARGS__) N_CASE(4, __VA_ARGS__) \
-                                        N_CASE(5, __VA_ARGS__) default: { const int N = (NV); __VA_ARGS__; } break; }
+#define N_SWITCH(NV, FALLBACK, ...) switch (NV) { N_CASE(1, __VA_ARGS__) N_CASE(2, __VA_ARGS__) N_CASE(3, __VA_ARGS__) N_CASE(4, __VA_ARGS__) \
+                                        N_CASE(5, __VA_ARGS__) default: { FALLBACK; } break; }
+static __device__ __noinline__ void big_init(plane_t* p, size_t W, int n, int active) { tab_init_word(p, W, 0, n, active); }
+static __device__ __noinline__ void big_gate(plane_t* p, size_t W, int n, int k, int q0, int q1, const uint8_t* om, uint32_t anf, uint32_t m) { tab_gate_anf(p, W, 0, n, k, q0, q1, om, anf, m); }
+static __device__ __noinline__ void big_noise(plane_t* p, size_t W, int n, int q, uint32_t fx, uint32_t fz) { tab_noise_apply(p, W, 0, n, q, fx, fz); }
+static __device__ __noinline__ uint32_t big_measure(plane_t* in, plane_t* out, size_t W, int n, int q, int tx, int tz, uint32_t rb, uint32_t* rnd) { return tab_measure_bits(in, out, W, 0, n, q, tx, tz, rb, rnd); }
+static __device__ __noinline__ void big_ptrace(plane_t* in, plane_t* out, size_t W, int n, int q) { tab_ptrace_word(in, out, W, 0, n, q); }
+static __device__ __noinline__ void big_force(plane_t* p, size_t W, int n, uint32_t px, uint32_t pz, int sign) { tab_force_word(p, W, 0, n, px, pz, sign); }
+static __device__ __noinline__ void big_expect(plane_t* p, size_t W, int n, const TabObsArgs& a, uint32_t* cnt, uint32_t* cntm) { tab_expect_word_n(p, W, 0, n, a, cnt, cntm); }
 
-// T == 1: the arena is a [planes][blockDim.x] tile of shared memory.  The block size is a RUN-TIME value (any thread count
+// T == 1: the arena is a [blockDim.x][tile_stride] tile of shared memory.  The block size is a RUN-TIME value (any thread count
 //         up to 256, partial last warp allowed) so that the host can size the blocks to cover the ensemble in whole waves
 //         (qsb_exec.cu: a 9 % tail wave used to double the run time).
 // T == 0: the arena is in global memory with stride `words` (programs whose tile exceeds the shared memory of an SM).
@@ -32,13 +42,17 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
     const uint32_t* const lanes = sjob.lanes;
     const size_t wg = (blockIdx.x - sjob.block0_exec) * (size_t)blockDim.x + threadIdx.x;   // word of the job (trajectories 32*wg ..)
     const bool on = wg < sjob.words;
-    plane_t* const base = T ? tile : sjob.arena;
-    const size_t W = T ? (size_t)blockDim.x : (size_t)sjob.words;
-    const size_t w = T ? (size_t)threadIdx.x : (on ? wg : 0);
+    // T == 1: the tile is [thread][tile_stride] -- a thread's planes are CONTIGUOUS (plane k at col[k]), so plane offsets fold
+    // into the immediate field of LDS/STS, distinct planes are provably distinct addresses (loads may be hoisted above stores:
+    // instruction-level parallelism inside an op body) and no address multiply is needed; tile_stride is odd, so the 32
+    // threads of a warp hit 32 different banks.  T == 0: plane-major global arena, plane k at col[k * words].
+    plane_t* const col = T ? tile + (size_t)threadIdx.x * (size_t)a.tile_stride : sjob.arena + (on ? wg : 0);
+    const size_t W = T ? (size_t)1 : (size_t)sjob.words;
+    const size_t w = 0;
     const uint32_t left = on ? sjob.count - (uint32_t)wg * 32u : 0u;
     const uint32_t validw = left >= 32u ? 0xffffffffu : ((1u << left) - 1u);
     uint32_t live = validw;
-#define PL(idx) (base + (size_t)(idx) * W)
+#define PL(idx) (col + (size_t)(idx) * W)
 #define LANE_ID(l) (lanes ? __ldg(lanes + wg * 32 + (l)) : (uint32_t)(wg * 32 + (l)))
     const uint32_t* const brow = sjob.bits + (on ? wg : 0) * (size_t)sjob.slot_stride;   // decision words of this thread's lanes
 #define DBITS(slot) (__ldg(brow + (slot)))
@@ -54,7 +68,7 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
         const ExecOp& op = sops[i % QSB_EXEC_CHUNK];
         switch (op.type) {
         case TOP_INIT:
-            if (on) { N_SWITCH(op.n, tab_init_word(PL(op.s[0]), W, w, N, op.iv[0])) PL(op.al[0])[w] = validw; }
+            if (on) { N_SWITCH(op.n, big_init(PL(op.s[0]), W, op.n, op.iv[0]), tab_init_word(PL(op.s[0]), W, w, N, op.iv[0])) PL(op.al[0])[w] = validw; }
             break;
         case TOP_TENSOR:
             if (on) {
@@ -104,30 +118,30 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
         case TOP_GATE:
             if (on) {
                 const uint32_t gm = op.m[0] >= 0 ? (uint32_t)PL(op.m[0])[w] : QSB_FULL;
-                N_SWITCH(op.n, tab_gate_anf(PL(op.s[0]), W, w, N, op.k, op.q[0], op.q[1], op.outmask, op.u[0], gm))
+                N_SWITCH(op.n, big_gate(PL(op.s[0]), W, op.n, op.k, op.q[0], op.q[1], op.outmask, op.u[0], gm), tab_gate_anf(PL(op.s[0]), W, w, N, op.k, op.q[0], op.q[1], op.outmask, op.u[0], gm))
             }
             break;
         case TOP_NOISE:
             if (on) {
                 const uint32_t fx = DBITS(op.dslot), fz = DBITS(op.dslot + 1);
-                N_SWITCH(op.n, tab_noise_apply(PL(op.s[0]), W, w, N, op.q[0], fx, fz))
+                N_SWITCH(op.n, big_noise(PL(op.s[0]), W, op.n, op.q[0], fx, fz), tab_noise_apply(PL(op.s[0]), W, w, N, op.q[0], fx, fz))
             }
             break;
         case TOP_MEASURE:
             if (on) {
                 uint32_t rnd;
                 uint32_t outcome = 0; const uint32_t rb = DBITS(op.dslot);
-                N_SWITCH(op.n, outcome = tab_measure_bits(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0], op.iv[0], op.iv[1], rb, &rnd))
+                N_SWITCH(op.n, outcome = big_measure(PL(op.s[1]), PL(op.s[0]), W, op.n, op.q[0], op.iv[0], op.iv[1], rb, &rnd), outcome = tab_measure_bits(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0], op.iv[0], op.iv[1], rb, &rnd))
                 uint32_t al = PL(op.al[1])[w];
                 PL(op.m[0])[w] = outcome & al;
                 if (op.m[1] >= 0) PL(op.m[1])[w] = rnd & al;
             }
             break;
         case TOP_PTRACE:
-            if (on) { N_SWITCH(op.n, tab_ptrace_word(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0])) }
+            if (on) { N_SWITCH(op.n, big_ptrace(PL(op.s[1]), PL(op.s[0]), W, op.n, op.q[0]), tab_ptrace_word(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0])) }
             break;
         case TOP_FORCE:
-            if (on) { N_SWITCH(op.n, tab_force_word(PL(op.s[0]), W, w, N, op.u[0], op.u[1], op.iv[0])) }
+            if (on) { N_SWITCH(op.n, big_force(PL(op.s[0]), W, op.n, op.u[0], op.u[1], op.iv[0]), tab_force_word(PL(op.s[0]), W, w, N, op.u[0], op.u[1], op.iv[0])) }
             break;
         case TOP_EXPECT: {
             // integer tallies (exact, order independent): alive lanes, sum of (plus - minus), sum of its square
@@ -137,7 +151,7 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
                 const TabObsArgs& o = sjob.obs[op.obs];
                 nelem = o.nelem;
                 uint32_t cnt[8], cntm[8];
-                N_SWITCH(op.n, tab_expect_word_n(PL(op.s[0]), W, w, N, o, cnt, cntm))
+                N_SWITCH(op.n, big_expect(PL(op.s[0]), W, op.n, o, cnt, cntm), tab_expect_word_n(PL(op.s[0]), W, w, N, o, cnt, cntm))
                 const uint32_t al = PL(op.al[0])[w] & live;   // retired lanes left this cohort: they are tallied where they continue
                 n_alive = __popc(al);
                 if (nelem == 1 && !op.per_traj) {   // a single Pauli: each lane holds -1, 0 or +1

@@ -39,8 +39,10 @@ struct ExecJob {
 struct WaveArgs {
     const ExecJob* jobs; int njobs;
     uint64_t seed, traj0, draw_base;   // global trajectory id of lane index 0, offset of every draw id
+    int tile_stride;                   // shared-memory executor: words per thread of the [thread][plane] tile (odd: conflict-free banks)
 };
 
 // launchers: [0] arena in global memory (one job per launch), [1] shared-memory tile with a run-time block size
 typedef cudaError_t (*qsb_exec_launch_fn)(const WaveArgs&, unsigned blocks, int threads, int smem_bytes, cudaStream_t stream);
 qsb_exec_launch_fn qsb_exec_launcher(int variant);
+static inline int qsb_exec_stride(int planes) { return planes | 1; }

@@ -14,6 +14,14 @@
 #define QSB_TAB_MAXN 32
 #endif
 #define MAXN QSB_TAB_MAXN
+// Every loop over rows / columns is marked for unrolling: the fused executor inlines these functions with a LITERAL qubit count,
+// and only fully unrolled loops keep the per-row scratch arrays (Analysis, pivots, products) in registers -- a rolled loop indexes
+// them dynamically, which puts them in local memory, and with the shared-memory carve-out at its maximum an LDL is an L2 round trip.
+#if defined(__CUDACC__)
+#define QSB_UNROLL _Pragma("unroll")
+#else
+#define QSB_UNROLL
+#endif
 // Storage type of one bit plane element: the number of trajectories ("lanes") one thread advances.  The per-op
 // kernels use 32-lane words; the fused executor (qsb_exec.cu) can compile this header with narrower planes (more threads
 // out of the same ensemble; see qsb_exec.cu).  Arithmetic is always done in 32-bit registers; QSB_FULL masks the lanes.
@@ -81,6 +89,7 @@ QSB_HD void row_mul(const TabView& v, int x0, int z0, int sgplane, uint32_t m,
                                         const uint32_t* sx, const uint32_t* sz, uint32_t ssign) {
     if (m == 0) return;
     uint32_t lo = 0, hi = 0;
+    QSB_UNROLL
     for (int c = 0; c < v.n; ++c) {
         uint32_t x1 = sx[c], z1 = sz[c];
         if ((x1 | z1) == 0) continue;
@@ -105,8 +114,10 @@ struct Analysis {
 // first active stabilizer that anticommutes, else an inactive (logical) row that anticommutes.
 QSB_HD void analyze(const TabView& v, uint32_t px, uint32_t pz, Analysis& A, uint32_t* pivD) {
     int n = v.n;
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) {
         uint32_t s = 0, d = 0;
+        QSB_UNROLL
         for (int c = 0; c < n; ++c) {
             if ((pz >> c) & 1) { s ^= v.ld(v.sx(i, c)); d ^= v.ld(v.dx(i, c)); }
             if ((px >> c) & 1) { s ^= v.ld(v.sz(i, c)); d ^= v.ld(v.dz(i, c)); }
@@ -114,8 +125,11 @@ QSB_HD void analyze(const TabView& v, uint32_t px, uint32_t pz, Analysis& A, uin
         A.acS[i] = s; A.acD[i] = d; A.act[i] = v.ld(v.ac(i));
     }
     uint32_t found = 0;
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) { A.piv[i] = A.acS[i] & A.act[i] & ~found; found |= A.piv[i]; }
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) { uint32_t t = A.acS[i] & ~A.act[i] & ~found; A.piv[i] |= t; found |= t; }
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) { uint32_t t = A.acD[i] & ~A.act[i] & ~found; pivD[i] = t; found |= t; }
     A.found = found;
 }
@@ -125,11 +139,14 @@ QSB_HD void analyze(const TabView& v, uint32_t px, uint32_t pz, Analysis& A, uin
 QSB_HD uint32_t determined_sign(const TabView& v, const Analysis& A, uint32_t det) {
     uint32_t accx[MAXN], accz[MAXN];
     int n = v.n;
+    QSB_UNROLL
     for (int c = 0; c < n; ++c) { accx[c] = 0; accz[c] = 0; }
     uint32_t lo = 0, hi = 0, sg = 0;
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) {
         uint32_t m = A.acD[i] & A.act[i] & det;
         if (m == 0) continue;
+        QSB_UNROLL
         for (int c = 0; c < n; ++c) {
             uint32_t x1 = v.ld(v.sx(i, c)) & m, z1 = v.ld(v.sz(i, c)) & m;
             uint32_t x2 = accx[c], z2 = accz[c];
@@ -155,9 +172,11 @@ QSB_HD uint32_t project_update(const TabView& v, uint32_t px, uint32_t pz, uint3
     uint32_t found = A.found, det = ~found & QSB_FULL;
     uint32_t dsign = determined_sign(v, A, det);
     // logical-row pivots found on a D row: exchange D_i and S_i there (both are logical operators)
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) {
         uint32_t m = pivD[i];
         if (m == 0) continue;
+        QSB_UNROLL
         for (int c = 0; c < n; ++c) {
             uint32_t a = v.ld(v.dx(i, c)), b = v.ld(v.sx(i, c)), t = (a ^ b) & m;
             v.st(v.dx(i, c), a ^ t); v.st(v.sx(i, c), b ^ t);
@@ -171,20 +190,26 @@ QSB_HD uint32_t project_update(const TabView& v, uint32_t px, uint32_t pz, uint3
     }
     if (found) {
         uint32_t pvx[MAXN], pvz[MAXN], pvs = 0;
+        QSB_UNROLL
         for (int c = 0; c < n; ++c) { pvx[c] = 0; pvz[c] = 0; }
+        QSB_UNROLL
         for (int i = 0; i < n; ++i) {
             uint32_t m = A.piv[i];
             if (m == 0) continue;
+            QSB_UNROLL
             for (int c = 0; c < n; ++c) { pvx[c] |= v.ld(v.sx(i, c)) & m; pvz[c] |= v.ld(v.sz(i, c)) & m; }
             pvs |= v.ld(v.sg(i)) & m;
         }
+        QSB_UNROLL
         for (int i = 0; i < n; ++i) {
             row_mul(v, v.sx(i, 0), v.sz(i, 0), v.sg(i), A.acS[i] & found & ~A.piv[i], pvx, pvz, pvs);
             row_mul(v, v.dx(i, 0), v.dz(i, 0), -1, A.acD[i] & found & ~A.piv[i], pvx, pvz, pvs);
         }
+        QSB_UNROLL
         for (int i = 0; i < n; ++i) {
             uint32_t m = A.piv[i];
             if (m == 0) continue;
+            QSB_UNROLL
             for (int c = 0; c < n; ++c) {
                 uint32_t pxc = ((px >> c) & 1) ? QSB_FULL : 0u, pzc = ((pz >> c) & 1) ? QSB_FULL : 0u;
                 v.st(v.dx(i, c), (v.ld(v.dx(i, c)) & ~m) | (pvx[c] & m));
@@ -200,20 +225,30 @@ QSB_HD uint32_t project_update(const TabView& v, uint32_t px, uint32_t pz, uint3
     if (settle && det) {
         // choose p = first active pair whose D anticommutes with P; D_i <- D_i D_p for the others; S_p <- +/-P
         uint32_t pd[MAXN], fd = 0;
+        QSB_UNROLL
         for (int i = 0; i < n; ++i) { pd[i] = A.acD[i] & A.act[i] & det & ~fd; fd |= pd[i]; }
         uint32_t dpx[MAXN], dpz[MAXN];
+        QSB_UNROLL
         for (int c = 0; c < n; ++c) { dpx[c] = 0; dpz[c] = 0; }
+        QSB_UNROLL
         for (int i = 0; i < n; ++i) {
             if (pd[i] == 0) continue;
+            QSB_UNROLL
             for (int c = 0; c < n; ++c) { dpx[c] |= v.ld(v.dx(i, c)) & pd[i]; dpz[c] |= v.ld(v.dz(i, c)) & pd[i]; }
         }
+        QSB_UNROLL
         for (int i = 0; i < n; ++i) {
             uint32_t m = A.acD[i] & A.act[i] & det & ~pd[i];
-            if (m) for (int c = 0; c < n; ++c) { v.st(v.dx(i, c), v.ld(v.dx(i, c)) ^ (dpx[c] & m)); v.st(v.dz(i, c), v.ld(v.dz(i, c)) ^ (dpz[c] & m)); }
+            if (m) {
+                QSB_UNROLL
+                for (int c = 0; c < n; ++c) { v.st(v.dx(i, c), v.ld(v.dx(i, c)) ^ (dpx[c] & m)); v.st(v.dz(i, c), v.ld(v.dz(i, c)) ^ (dpz[c] & m)); }
+            }
         }
+        QSB_UNROLL
         for (int i = 0; i < n; ++i) {
             uint32_t m = pd[i];
             if (m == 0) continue;
+            QSB_UNROLL
             for (int c = 0; c < n; ++c) {
                 uint32_t pxc = ((px >> c) & 1) ? QSB_FULL : 0u, pzc = ((pz >> c) & 1) ? QSB_FULL : 0u;
                 v.st(v.sx(i, c), (v.ld(v.sx(i, c)) & ~m) | (pxc & m));
@@ -230,17 +265,21 @@ QSB_HD uint32_t project_update(const TabView& v, uint32_t px, uint32_t pz, uint3
 // S_piv (= +/-P_q) clears it and only touches the sign; pair n-1 moves into the pivot's slot.
 QSB_HD void remove_qubit(const TabView& v, const TabView& o, int q, const Analysis& A, uint32_t outcome, uint32_t skip_sign_fix) {
     int n = v.n;
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) {
         uint32_t nz = (v.ld(v.sx(i, q)) | v.ld(v.sz(i, q))) & ~A.piv[i] & ~skip_sign_fix;
         if (nz & outcome) v.st(v.sg(i), v.ld(v.sg(i)) ^ (nz & outcome));
     }
     int last = n - 1;
+    QSB_UNROLL
     for (int i = 0; i < n - 1; ++i) {
         uint32_t m = A.piv[i];  // lanes whose pivot sits here take pair `last`
         // plane order (pair, kind, column) ascending on both sides: every write lands at or below the plane
         // just read, so `o` may alias `v` (in-place shrink inside a recorded program's arena)
+        QSB_UNROLL
         for (int kind = 0; kind < 4; ++kind) {
             int cc = 0;
+            QSB_UNROLL
             for (int c = 0; c < n; ++c) {
                 if (c == q) continue;
                 o.st(i * o.S + kind * (n - 1) + cc, (v.ld(i * v.S + kind * n + c) & ~m) | (v.ld(last * v.S + kind * n + c) & m));
@@ -265,7 +304,9 @@ QSB_HD uint32_t lane_bits_ge_half(uint64_t seed, uint64_t traj0, size_t w, uint6
 // ---------------------------------------------------------------------------------------------
 QSB_HD void tab_init_word(plane_t* p, size_t W, size_t w, int n, int active) {
     TabView v = make_view(p, W, w, n);
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) {
+        QSB_UNROLL
         for (int c = 0; c < n; ++c) {
             v.st(v.dx(i, c), c == i ? QSB_FULL : 0u); v.st(v.dz(i, c), 0u);
             v.st(v.sx(i, c), 0u); v.st(v.sz(i, c), c == i ? QSB_FULL : 0u);
@@ -278,9 +319,11 @@ QSB_HD void tab_init_word(plane_t* p, size_t W, size_t w, int n, int active) {
 QSB_HD void tab_tensor_word(plane_t* out, const plane_t* a, const plane_t* b, size_t W, size_t w, int na, int nb) {
     int n = na + nb;
     TabView o = make_view(out, W, w, n), va = make_view((plane_t*)a, W, w, na), vb = make_view((plane_t*)b, W, w, nb);
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) {
         bool fa = i < na;
         int j = fa ? i : i - na;
+        QSB_UNROLL
         for (int c = 0; c < n; ++c) {
             bool in_a = c < na;
             uint32_t dxv = 0, dzv = 0, sxv = 0, szv = 0;
@@ -320,17 +363,22 @@ QSB_HD void tab_gate_rows(const TabView& v, int q0, int q1, const uint8_t* om, u
     constexpr int NB = 2 * K;
     const int n = v.n;
     uint32_t chg = 0;
+    QSB_UNROLL
     for (int b = 0; b < NB; ++b) if (om[b] != (1u << b)) chg |= 1u << b;
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) {
+        QSB_UNROLL
         for (int half = 0; half < 2; ++half) {
             if (!half && !chg) continue;                      // Pauli gates touch signs only
             const int xb = i * v.S + half * 2 * n, zb = xb + n;
             uint32_t in[NB];
             in[0] = v.ld(xb + q0); in[1] = v.ld(zb + q0);
             if (K == 2) { in[NB - 2] = v.ld(xb + q1); in[NB - 1] = v.ld(zb + q1); }
+            QSB_UNROLL
             for (int b = 0; b < NB; ++b) {
                 if (!((chg >> b) & 1)) continue;
                 uint32_t o = 0;
+                QSB_UNROLL
                 for (int j = 0; j < NB; ++j) o ^= ((om[b] >> j) & 1) ? in[j] : 0u;
                 v.st(((b & 1) ? zb : xb) + ((b >> 1) ? q1 : q0), in[b] ^ ((in[b] ^ o) & m));
             }
@@ -339,6 +387,7 @@ QSB_HD void tab_gate_rows(const TabView& v, int q0, int q1, const uint8_t* om, u
                 for (uint32_t t = anf; t; t &= t - 1) {
                     const int k = qsb_ctz32(t);
                     uint32_t term = QSB_FULL;
+                    QSB_UNROLL
                     for (int j = 0; j < NB; ++j) term &= ((k >> j) & 1) ? in[j] : QSB_FULL;
                     flip ^= term;
                 }
@@ -373,6 +422,7 @@ QSB_HD uint32_t tab_noise_decide(const TabNoiseArgs& a, double r) {
 QSB_HD void tab_noise_apply(plane_t* p, size_t W, size_t w, int n, int q, uint32_t fx, uint32_t fz) {
     if ((fx | fz) == 0) return;
     TabView v = make_view(p, W, w, n);
+    QSB_UNROLL
     for (int i = 0; i < n; ++i) {  // sign of S_i flips where it anticommutes with the applied Pauli
         uint32_t flip = (v.ld(v.sx(i, q)) & fz) ^ (v.ld(v.sz(i, q)) & fx);
         if (flip) v.st(v.sg(i), v.ld(v.sg(i)) ^ flip);
@@ -418,23 +468,31 @@ QSB_HD void tab_ptrace_word(plane_t* in, plane_t* out, size_t W, size_t w, int n
     if (rnd) {
         // the other stabilizers with Z on q only survive in pairs: keep products with the first one, which is lost
         uint32_t pj[MAXN], fj = 0;
+        QSB_UNROLL
         for (int i = 0; i < n; ++i) { pj[i] = A.act[i] & v.ld(v.sz(i, q)) & ~A.piv[i] & rnd & ~fj; fj |= pj[i]; }
         if (fj) {
             uint32_t jx[MAXN], jz[MAXN], js = 0, dax[MAXN], daz[MAXN];
+            QSB_UNROLL
             for (int c = 0; c < n; ++c) { jx[c] = 0; jz[c] = 0; dax[c] = 0; daz[c] = 0; }
+            QSB_UNROLL
             for (int i = 0; i < n; ++i) {
                 if (pj[i] == 0) continue;
+                QSB_UNROLL
                 for (int c = 0; c < n; ++c) { jx[c] |= v.ld(v.sx(i, c)) & pj[i]; jz[c] |= v.ld(v.sz(i, c)) & pj[i]; }
                 js |= v.ld(v.sg(i)) & pj[i];
             }
+            QSB_UNROLL
             for (int k = 0; k < n; ++k) {
                 uint32_t mk = A.act[k] & v.ld(v.sz(k, q)) & ~A.piv[k] & ~pj[k] & fj;
                 if (mk == 0) continue;
+                QSB_UNROLL
                 for (int c = 0; c < n; ++c) { dax[c] ^= v.ld(v.dx(k, c)) & mk; daz[c] ^= v.ld(v.dz(k, c)) & mk; }
                 row_mul(v, v.sx(k, 0), v.sz(k, 0), v.sg(k), mk, jx, jz, js);
             }
+            QSB_UNROLL
             for (int i = 0; i < n; ++i) {
                 if (pj[i] == 0) continue;
+                QSB_UNROLL
                 for (int c = 0; c < n; ++c) { v.st(v.dx(i, c), v.ld(v.dx(i, c)) ^ (dax[c] & pj[i])); v.st(v.dz(i, c), v.ld(v.dz(i, c)) ^ (daz[c] & pj[i])); }
                 v.st(v.ac(i), v.ld(v.ac(i)) & ~pj[i]);
             }
