@@ -23,7 +23,8 @@
 // one stochastic op of the program as the draw pass sees it
 struct DrawSpec {
     uint64_t draw;
-    int type, np, slot, pad;   // type: TOP_NOISE / TOP_SELECT / TOP_MEASURE / TOP_MASK_RANDOM
+    int type, np, slot;        // type: TOP_NOISE / TOP_SELECT / TOP_MEASURE / TOP_MASK_RANDOM
+    uint32_t thr_hi_any;       // noise: high word of ((thr_any + 1) << 11) -- hi32(draw bits) < thr_hi_any on every lane proves "no error in this word"
     // the comparisons of the per-op kernels (u = k / 2^53 against a double c) restated EXACTLY on the 53-bit integer k:
     //   u > c  <=>  k > floor(c * 2^53)        u < c  <=>  k < ceil(c * 2^53)        (c * 2^53 is exact in a double)
     uint64_t thr[5];
@@ -32,11 +33,24 @@ struct DrawSpec {
     int pad2;
 };
 #define QSB_DRAW_CHUNK 64      // specs staged per shared-memory refill of the draw pass
+// The draw pass's work list: one item per Philox block (= two consecutive draw ids), so a block is computed once and its two
+// halves are consumed without any "is this block already in registers" test.  32 bytes = two 128-bit shared-memory loads.
+enum { DK_NONE = 0, DK_NOISE = 1, DK_SELECT = 2, DK_MEASURE = 3, DK_MASK = 4 };
+struct DrawItem {
+    uint32_t blk;          // draw id >> 1 (before draw_base)
+    uint32_t kinds;        // kind of half 0 | kind of half 1 << 8
+    uint32_t spec[2];      // index into the DrawSpec table (exact thresholds: read only on the slow paths)
+    uint32_t thr_hi[2];    // DK_NOISE: DrawSpec::thr_hi_any
+    uint32_t slot[2];      // first decision slot
+};
+static_assert(sizeof(DrawItem) == 32, "DrawItem layout");
+#define QSB_ITEM_CHUNK 64      // items staged per refill: at most 2 * 3 slots each
 
 struct qsb_program {
     qsb_ctx* ctx;
     qsb_dprogram* dprog;   // non-null: a dense program (qsb_dexec.cu); the tableau fields below are unused except d_stats
-    DrawSpec* d_specs; int nspecs, nslots, slot_stride;
+    DrawSpec* d_specs; int nspecs, nslots, first_dslot;
+    DrawItem* d_items; int nitems;
     uint8_t* d_aux; int naux, nfolded;   // constant tables of folded ops
     ExecOp* d_ops; int nops;
     TabObsArgs* d_obs; int nobs;
@@ -160,8 +174,14 @@ __global__ void k_zero_stats(double* const* ptrs, int n) {
 // thread-per-word kernel would have to loop over its 32 lanes for, at 1/32 of the parallelism).
 // Like the executor it runs any number of (program, lane subset) jobs per launch: block b belongs to the job with the
 // largest block0_draw <= b, thread t of a job draws for the trajectory whose lane index is lanes[t] (identity when null).
+// Output layout bits[slot][wstride] (slot-major).  A block is 8 warps = 8 consecutive words = ONE 32-byte sector of every
+// slot row: the decision words of a chunk of specs are collected in shared memory [slot][8] and written sector by sector.
+// Noise specs take a fast path: "no error on any lane of this word" (the common case at small p) follows from the HIGH 32
+// bits of the draw alone (hi < thr_hi_any on all 32 lanes); only otherwise are the exact 53-bit comparisons evaluated.
+#define QSB_DRAW_MAXSLOTS (3 * QSB_DRAW_CHUNK)
 __global__ void __launch_bounds__(256) k_draw_bits(WaveArgs a) {
     __shared__ __align__(16) DrawSpec sspec[QSB_DRAW_CHUNK];   // filled with 16-byte copies
+    __shared__ __align__(16) uint32_t sbits[QSB_DRAW_MAXSLOTS][8];
     __shared__ ExecJob sjob;
     if (threadIdx.x == 0) {
         int lo = 0, hi = a.njobs - 1;
@@ -170,51 +190,155 @@ __global__ void __launch_bounds__(256) k_draw_bits(WaveArgs a) {
     }
     __syncthreads();
     const DrawSpec* const specs = reinterpret_cast<const DrawSpec*>(sjob.specs);
-    const int nspecs = sjob.nspecs, slot_stride = sjob.slot_stride;
-    const size_t t = (blockIdx.x - sjob.block0_draw) * (size_t)blockDim.x + threadIdx.x;   // trajectory of the job; words*32 is a multiple of 32
-    const bool on = t < (size_t)sjob.words * 32;                      // whole warps are on or off together
-    const unsigned lane = threadIdx.x & 31u;
-    uint32_t* row = sjob.bits + (on ? (t >> 5) : 0) * (size_t)slot_stride; // this word's slots are contiguous: slot order = spec order
-    // decision words wait in registers (lane l holds the l-th pending word) until 32 of them go out as one 128-byte store
-    uint32_t mine = 0;
-    unsigned fill = 0;
+    const int nspecs = sjob.nspecs;
+    const size_t t = (blockIdx.x - sjob.block0_draw) * (size_t)blockDim.x + threadIdx.x;   // trajectory of the job
+    const unsigned lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;                      // warp in block = word in the sector
+    const size_t word0 = (blockIdx.x - sjob.block0_draw) * (size_t)8;                      // first word of this block
     const uint64_t traj = a.traj0 + ((sjob.lanes && t < sjob.count) ? (uint64_t)__ldg(sjob.lanes + t) : (uint64_t)t);
     uint32_t blk[4];
     uint64_t have = ~0ull;   // Philox block currently in registers (two draws per block)
-    auto push = [&](uint32_t word) {
-        if (lane == fill) mine = word;
-        if (++fill == 32) { if (on) row[lane] = mine; row += 32; fill = 0; }
-    };
     for (int i0 = 0; i0 < nspecs; i0 += QSB_DRAW_CHUNK) {
-        __syncthreads();
+        __syncthreads();     // the previous chunk's words have been written out
         const int nc = min(QSB_DRAW_CHUNK, nspecs - i0);
         for (int k = threadIdx.x; k < nc * (int)(sizeof(DrawSpec) / 16); k += blockDim.x)
             reinterpret_cast<uint4*>(sspec)[k] = __ldg(reinterpret_cast<const uint4*>(specs + i0) + k);
         __syncthreads();
+        const int slot0 = sspec[0].slot;
         for (int i = 0; i < nc; ++i) {
             const DrawSpec& s = sspec[i];
             const uint64_t id = s.draw + a.draw_base;
             if ((id >> 1) != have) { have = id >> 1; qsb_philox_block(a.seed, traj, have, blk); }
-            const uint64_t k = ((id & 1) ? (((uint64_t)blk[3] << 32) | blk[2]) : (((uint64_t)blk[1] << 32) | blk[0])) >> 11;   // u = k / 2^53
-            if (s.type == TOP_NOISE) {
-                if (!__any_sync(0xffffffffu, k > s.thr_any)) { push(0u); push(0u); continue; }   // the common case: nobody errs
+            const uint32_t xlo = (id & 1) ? blk[2] : blk[0], xhi = (id & 1) ? blk[3] : blk[1];
+            uint32_t* const out = &sbits[s.slot - slot0][wib];
+            const int type = s.type;
+            if (type == TOP_NOISE) {
+                if (!__any_sync(0xffffffffu, xhi >= s.thr_hi_any)) { if (lane == 0) { out[0] = 0u; out[8] = 0u; } continue; }   // nobody errs
+                const uint64_t k = (((uint64_t)xhi << 32) | xlo) >> 11;   // u = k / 2^53
                 uint32_t d = 0;
                 for (int j = s.np - 1; j >= 0; --j) if (k > s.thr[j]) d = s.code[j];   // first matching branch wins (thr descends)
-                push(__ballot_sync(0xffffffffu, d & 1u));
-                push(__ballot_sync(0xffffffffu, d & 2u));
-            } else if (s.type == TOP_SELECT) {
+                const uint32_t fx = __ballot_sync(0xffffffffu, d & 1u), fz = __ballot_sync(0xffffffffu, d & 2u);
+                if (lane == 0) { out[0] = fx; out[8] = fz; }
+            } else if (type == TOP_SELECT) {
+                const uint64_t k = (((uint64_t)xhi << 32) | xlo) >> 11;
                 uint32_t d = (uint32_t)(s.np - 1);
                 for (int j = s.np - 2; j >= 0; --j) if (k < s.thr[j]) d = (uint32_t)j;           // first j with u < cum[j]
-                push(__ballot_sync(0xffffffffu, d & 1u));
-                push(__ballot_sync(0xffffffffu, d & 2u));
-                push(__ballot_sync(0xffffffffu, d & 4u));
+                const uint32_t b0 = __ballot_sync(0xffffffffu, d & 1u), b1 = __ballot_sync(0xffffffffu, d & 2u), b2 = __ballot_sync(0xffffffffu, d & 4u);
+                if (lane == 0) { out[0] = b0; out[8] = b1; out[16] = b2; }
+            } else if (type == TOP_MEASURE) {
+                const uint32_t b = __ballot_sync(0xffffffffu, xhi >> 31);     // !(u < 0.5)  <=>  top bit of the draw
+                if (lane == 0) out[0] = b;
             } else {
-                const bool below = k < s.thr[0];   // measurement: thr = 2^52, bit = !(u < 0.5); random mask: bit = u < p
-                push(__ballot_sync(0xffffffffu, s.type == TOP_MEASURE ? !below : below));
+                const uint64_t k = (((uint64_t)xhi << 32) | xlo) >> 11;
+                const uint32_t b = __ballot_sync(0xffffffffu, k < s.thr[0]);  // random mask: bit = u < p
+                if (lane == 0) out[0] = b;
             }
         }
+        __syncthreads();
+        // write the chunk: slot row r, words word0 .. word0 + 7 = one aligned 32-byte sector
+        const DrawSpec& last = sspec[nc - 1];
+        const int nsl = last.slot - slot0 + (last.type == TOP_NOISE ? 2 : last.type == TOP_SELECT ? 3 : 1);
+        for (int k = threadIdx.x; k < nsl * 8; k += blockDim.x) {
+            const size_t wd = word0 + (k & 7);
+            if (wd < sjob.wstride) sjob.bits[(size_t)(slot0 + (k >> 3)) * sjob.wstride + wd] = sbits[k >> 3][k & 7];
+        }
     }
-    if (on && lane < fill) row[lane] = mine;
+}
+
+// The same pass over the item list (one Philox block per trip, both halves consumed in place): the default whenever
+// draw_base is even, i.e. whenever the pairing of draw ids into blocks is the one the items were built for.
+// Philox4x32-10 with the round keys taken from the kernel arguments (constant bank): 20 IMAD.WIDE + 20 LOP3 per block
+__device__ __forceinline__ void philox_rk(const uint32_t (&rk)[20], uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t* out) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ rk[2 * r], n2 = (uint32_t)(p0 >> 32) ^ c3 ^ rk[2 * r + 1];
+        c0 = n0; c1 = (uint32_t)p1; c2 = n2; c3 = (uint32_t)p0;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+__global__ void __launch_bounds__(256) k_draw_items(const __grid_constant__ WaveArgs a) {
+    __shared__ __align__(16) DrawItem sitem[QSB_ITEM_CHUNK];
+    __shared__ __align__(16) uint32_t sbits[6 * QSB_ITEM_CHUNK][8];
+    __shared__ ExecJob sjob;
+    if (threadIdx.x == 0) {
+        int lo = 0, hi = a.njobs - 1;
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (a.jobs[mid].block0_draw <= blockIdx.x) lo = mid; else hi = mid - 1; }
+        sjob = a.jobs[lo];
+    }
+    __syncthreads();
+    const DrawItem* const items = reinterpret_cast<const DrawItem*>(sjob.items);
+    const DrawSpec* const specs = reinterpret_cast<const DrawSpec*>(sjob.specs);
+    const int nitems = sjob.nitems;
+    const size_t t = (blockIdx.x - sjob.block0_draw) * (size_t)blockDim.x + threadIdx.x;   // trajectory of the job
+    const unsigned lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;                      // warp in block = word in the sector
+    const size_t word0 = (blockIdx.x - sjob.block0_draw) * (size_t)8;
+    const uint64_t traj = a.traj0 + ((sjob.lanes && t < sjob.count) ? (uint64_t)__ldg(sjob.lanes + t) : (uint64_t)t);
+    const uint64_t blk_base = a.draw_base >> 1;
+    auto nslots_of = [](uint32_t kind) { return kind == DK_NOISE ? 2u : kind == DK_SELECT ? 3u : kind == DK_NONE ? 0u : 1u; };
+    for (int i0 = 0; i0 < nitems; i0 += QSB_ITEM_CHUNK) {
+        __syncthreads();     // the previous chunk's words have been written out
+        const int nc = min(QSB_ITEM_CHUNK, nitems - i0);
+        for (int k = threadIdx.x; k < nc * 2; k += blockDim.x) reinterpret_cast<uint4*>(sitem)[k] = __ldg(reinterpret_cast<const uint4*>(items + i0) + k);
+        __syncthreads();
+        const uint32_t slot0 = (sitem[0].kinds & 0xff) ? sitem[0].slot[0] : sitem[0].slot[1];
+        uint32_t* const mine = &sbits[0][wib] - (size_t)slot0 * 8;   // word `wib` of slot s lives at mine[s * 8]
+#pragma unroll 1
+        for (int i = 0; i < nc; ++i) {
+            const uint4 lo4 = reinterpret_cast<const uint4*>(sitem)[2 * i], hi4 = reinterpret_cast<const uint4*>(sitem)[2 * i + 1];
+            uint32_t blk[4];
+            const uint64_t bno = blk_base + lo4.x;
+            philox_rk(a.rk, (uint32_t)traj, (uint32_t)(traj >> 32), (uint32_t)bno, (uint32_t)(bno >> 32), blk);
+            if (lo4.y == (DK_NOISE | (DK_NOISE << 8))) {   // both halves are noise draws (two thirds of the items): no per-half dispatch
+                const bool e0 = __any_sync(0xffffffffu, blk[1] >= hi4.x), e1 = __any_sync(0xffffffffu, blk[3] >= hi4.y);
+                if (!(e0 | e1)) {
+                    if (lane == 0) { uint32_t* o0 = mine + (size_t)hi4.z * 8; uint32_t* o1 = mine + (size_t)hi4.w * 8; o0[0] = 0u; o0[8] = 0u; o1[0] = 0u; o1[8] = 0u; }
+                    continue;
+                }
+            }
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t kind = (lo4.y >> (8 * h)) & 0xffu;
+                if (kind == DK_NONE) continue;
+                const uint32_t xlo = h ? blk[2] : blk[0], xhi = h ? blk[3] : blk[1];
+                const uint32_t thr_hi = h ? hi4.y : hi4.x, slot = h ? hi4.w : hi4.z, sidx = h ? lo4.w : lo4.z;
+                uint32_t* const out = mine + (size_t)slot * 8;
+                if (kind == DK_NOISE) {
+                    if (!__any_sync(0xffffffffu, xhi >= thr_hi)) { if (lane == 0) { out[0] = 0u; out[8] = 0u; } continue; }   // nobody errs
+                    const DrawSpec* sp = specs + sidx;
+                    const uint64_t k = (((uint64_t)xhi << 32) | xlo) >> 11;   // u = k / 2^53
+                    const int np = __ldg(&sp->np);
+                    uint32_t d = 0;
+                    for (int j = np - 1; j >= 0; --j) if (k > __ldg(&sp->thr[j])) d = __ldg(&sp->code[j]);   // first matching branch wins (thr descends)
+                    const uint32_t fx = __ballot_sync(0xffffffffu, d & 1u), fz = __ballot_sync(0xffffffffu, d & 2u);
+                    if (lane == 0) { out[0] = fx; out[8] = fz; }
+                } else if (kind == DK_MEASURE) {
+                    const uint32_t b = __ballot_sync(0xffffffffu, xhi >> 31);     // !(u < 0.5)  <=>  top bit of the draw
+                    if (lane == 0) out[0] = b;
+                } else if (kind == DK_SELECT) {
+                    const DrawSpec* sp = specs + sidx;
+                    const uint64_t k = (((uint64_t)xhi << 32) | xlo) >> 11;
+                    const int np = __ldg(&sp->np);
+                    uint32_t d = (uint32_t)(np - 1);
+                    for (int j = np - 2; j >= 0; --j) if (k < __ldg(&sp->thr[j])) d = (uint32_t)j;           // first j with u < cum[j]
+                    const uint32_t b0 = __ballot_sync(0xffffffffu, d & 1u), b1 = __ballot_sync(0xffffffffu, d & 2u), b2 = __ballot_sync(0xffffffffu, d & 4u);
+                    if (lane == 0) { out[0] = b0; out[8] = b1; out[16] = b2; }
+                } else {
+                    const uint64_t k = (((uint64_t)xhi << 32) | xlo) >> 11;
+                    const uint32_t b = __ballot_sync(0xffffffffu, k < __ldg(&(specs + sidx)->thr[0]));  // random mask: bit = u < p
+                    if (lane == 0) out[0] = b;
+                }
+            }
+        }
+        __syncthreads();
+        const DrawItem& last = sitem[nc - 1];
+        const uint32_t kb = (last.kinds >> 8) & 0xff, ka = last.kinds & 0xff;
+        const uint32_t end = kb ? last.slot[1] + nslots_of(kb) : last.slot[0] + nslots_of(ka);
+        const int nsl = (int)(end - slot0);
+        for (int k = threadIdx.x; k < nsl * 8; k += blockDim.x) {
+            const size_t wd = word0 + (k & 7);
+            if (wd < sjob.wstride) sjob.bits[(size_t)(slot0 + (k >> 3)) * sjob.wstride + wd] = sbits[k >> 3][k & 7];
+        }
+    }
 }
 
 // the two instantiations live in qsb_exec_inst.cu (one object each, csrc/Makefile)
@@ -459,11 +583,38 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
                 if (d.thr[j] < d.thr_any) d.thr_any = d.thr[j];
                 d.code[j] = (uint8_t)(((o.iv[j] == 1 || o.iv[j] == 2) ? 1 : 0) | ((o.iv[j] == 3 || o.iv[j] == 2) ? 2 : 0));
             }
+            // k > thr_any  <=>  x >= (thr_any + 1) << 11 for the 64 draw bits x (k = x >> 11); thr_any + 1 = 2^53 can never be reached
+            const uint64_t t1 = d.thr_any + 1;
+            d.thr_hi_any = (d.np == 0 || t1 >= (1ull << 53)) ? 0xffffffffu : (uint32_t)((t1 << 11) >> 32);
+            if (d.np == 0) d.thr_any = ~0ull;
         }
         o.dslot = P->nslots; P->nslots += need;
         specs.push_back(d);
     }
     P->nspecs = (int)specs.size();
+    std::vector<DrawItem> items;
+    for (size_t i = 0; i < specs.size(); ++i) {
+        const DrawSpec& d = specs[i];
+        const uint32_t blk = (uint32_t)(d.draw >> 1), half = (uint32_t)(d.draw & 1);
+        if (items.empty() || items.back().blk != blk || ((items.back().kinds >> (8 * half)) & 0xff)) {
+            DrawItem it; memset(&it, 0, sizeof(it)); it.blk = blk; items.push_back(it);
+        }
+        DrawItem& it = items.back();
+        const uint32_t kind = d.type == TOP_NOISE ? DK_NOISE : d.type == TOP_SELECT ? DK_SELECT : d.type == TOP_MEASURE ? DK_MEASURE : DK_MASK;
+        it.kinds |= kind << (8 * half); it.spec[half] = (uint32_t)i; it.thr_hi[half] = d.thr_hi_any; it.slot[half] = (uint32_t)d.slot;
+    }
+    P->nitems = (int)items.size();
+    P->first_dslot = -1;
+    {   // every stochastic op names the slots of the next one: the executor fetches decision words one stochastic op ahead
+        int next = -1;
+        for (size_t i = R->ops.size(); i-- > 0;) {
+            TabOp& o = R->ops[i];
+            const bool stoch = o.type == TOP_NOISE || o.type == TOP_SELECT || o.type == TOP_SELECT_CONST || o.type == TOP_MEASURE || o.type == TOP_MASK_RANDOM;
+            o.lut = (uint32_t)next;          // host-only field, free at this point: carries next_dslot into the ExecOp
+            if (stoch) next = o.dslot;
+        }
+        P->first_dslot = next;
+    }
     // the kernel's compact op records
     std::vector<ExecOp> xops(R->ops.size());
     for (size_t i = 0; i < R->ops.size() && rc == QSB_OK; ++i) {
@@ -477,10 +628,8 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
         x.u[0] = o.u[0]; x.u[1] = o.u[1];
         for (int j = 0; j < 6; ++j) { x.s[j] = (int16_t)o.s[j]; x.al[j] = (int16_t)o.al[j]; }
         for (int j = 0; j < 3; ++j) x.m[j] = (int16_t)o.m[j];
-        x.obs = o.obs; x.dslot = o.dslot; x.stats = o.stats; x.per_traj = o.per_traj;
+        x.obs = o.obs; x.dslot = o.dslot; x.next_dslot = (int32_t)o.lut; x.stats = o.stats; x.per_traj = o.per_traj;
     }
-    P->slot_stride = (P->nslots + 7) / 8 * 8;   // rows start on a 32-byte sector
-    if (P->slot_stride == 0) P->slot_stride = 8;
     if (!xops.empty() && rc == QSB_OK) {
         if (cudaMallocHost((void**)&P->h_ops, xops.size() * sizeof(ExecOp)) != cudaSuccess) { cudaGetLastError(); qsb_set_error("pinned allocation of the op list failed"); rc = QSB_ERR_OOM; }
         else memcpy(P->h_ops, xops.data(), xops.size() * sizeof(ExecOp));
@@ -497,6 +646,7 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     up((void**)&P->d_obs, R->obs.data(), R->obs.size() * sizeof(TabObsArgs));
     up((void**)&P->d_stats, R->stats_ptrs.data(), R->stats_ptrs.size() * sizeof(double*));
     up((void**)&P->d_specs, specs.data(), specs.size() * sizeof(DrawSpec));
+    up((void**)&P->d_items, items.data(), items.size() * sizeof(DrawItem));
     up((void**)&P->d_aux, aux.data(), aux.size());
     if (rc == QSB_OK) { cudaError_t e = cudaStreamSynchronize(ctx->stream); if (e != cudaSuccess) rc = QSB_ERR_CUDA; }  // host vectors die below
     // launch shape of the full-ensemble replay (reported by qsb_program_info; subsets and waves are shaped at run time)
@@ -561,7 +711,7 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
     for (int j = 0; j < n; ++j) {
         qsb_program* P = in[j].P;
         words[j] = (uint32_t)((in[j].count + 31) / 32);
-        bits_words += (size_t)words[j] * P->slot_stride;
+        bits_words += (size_t)(P->nslots + 4) * ((words[j] + 7u) & ~7u);   // +4 rows: the executor's read-ahead may run past the last slot
         planes = std::max(planes, P->planes);
         nspecs_any |= P->nspecs;
     }
@@ -580,11 +730,13 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
         qsb_program* P = in[j].P;
         ExecJob& J = jobs[j];
         J.ops = P->d_ops; J.obs = P->d_obs; J.aux = P->d_aux; J.specs = P->d_specs; J.lanes = in[j].lanes;
+        J.items = P->d_items; J.nitems = P->nitems; J.pad_items = 0;
         J.bits = ctx->wave_bits + boff; J.arena = (uint32_t*)P->arena;
-        J.nops = P->nops; J.nspecs = P->nspecs; J.slot_stride = P->slot_stride; J.planes = P->planes;
+        J.nops = P->nops; J.nspecs = P->nspecs; J.nslots = P->nslots; J.planes = P->planes;
+        J.wstride = (words[j] + 7u) & ~7u; J.first_dslot = P->first_dslot;
         J.count = (uint32_t)in[j].count; J.words = words[j];
         J.block0_exec = be; J.block0_draw = bd;
-        boff += (size_t)words[j] * P->slot_stride;
+        boff += (size_t)(P->nslots + 4) * J.wstride;
         be += (words[j] + threads - 1) / threads;
         bd += P->nspecs ? (uint32_t)(((size_t)words[j] * 32 + 255) / 256) : 0u;
     }
@@ -594,9 +746,11 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
     a.jobs = (const ExecJob*)ctx->wave_jobs; a.njobs = n;
     a.seed = ctx->seed; a.traj0 = (uint64_t)ctx->traj_offset + traj_shift; a.draw_base = draw_base;
     a.tile_stride = qsb_exec_stride(planes);
+    for (int r = 0; r < 10; ++r) { a.rk[2 * r] = (uint32_t)ctx->seed + (uint32_t)r * 0x9E3779B9u; a.rk[2 * r + 1] = (uint32_t)(ctx->seed >> 32) + (uint32_t)r * 0xBB67AE85u; }
     if (bd) {
         QSB_PRE(ctx, "k_draw_bits");
-        k_draw_bits<<<bd, 256, 0, ctx->stream>>>(a);
+        if (draw_base & 1) k_draw_bits<<<bd, 256, 0, ctx->stream>>>(a);   // odd offset: the items' pairing of draws into blocks does not apply
+        else k_draw_items<<<bd, 256, 0, ctx->stream>>>(a);
         QSB_LAUNCH_CHECK(ctx);
     }
     if (be) {
@@ -689,7 +843,7 @@ extern "C" int qsb_program_free(qsb_program* P) {
     qsb_ctx* ctx = P->ctx;
     if (P->dprog) { qsb_dexec_free(P->dprog); qsb_dev_free(ctx, P->d_stats); delete P; return QSB_OK; }
     qsb_dev_free(ctx, P->d_ops); qsb_dev_free(ctx, P->d_obs); qsb_dev_free(ctx, P->d_stats);
-    qsb_dev_free(ctx, P->d_specs); qsb_dev_free(ctx, P->d_aux);
+    qsb_dev_free(ctx, P->d_specs); qsb_dev_free(ctx, P->d_items); qsb_dev_free(ctx, P->d_aux);
     if (P->arena) qsb_dev_free(ctx, P->arena);
     if (P->h_ops) cudaFreeHost(P->h_ops);
     delete P;

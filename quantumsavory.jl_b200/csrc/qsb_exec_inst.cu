@@ -54,8 +54,15 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
     uint32_t live = validw;
 #define PL(idx) (col + (size_t)(idx) * W)
 #define LANE_ID(l) (lanes ? __ldg(lanes + wg * 32 + (l)) : (uint32_t)(wg * 32 + (l)))
-    const uint32_t* const brow = sjob.bits + (on ? wg : 0) * (size_t)sjob.slot_stride;   // decision words of this thread's lanes
-#define DBITS(slot) (__ldg(brow + (slot)))
+    // decision words: bits[slot][wstride], this thread's column; a warp reads one 128-byte line per slot.  The three words of
+    // the NEXT stochastic op are fetched while the current one executes (ExecOp::next_dslot), so their latency is off the
+    // critical path; DBITS(j) is word j of the current stochastic op.
+    const uint32_t* const bcol = sjob.bits + (on ? wg : 0);
+    const size_t bstride = sjob.wstride;
+    uint32_t pre0 = 0, pre1 = 0, pre2 = 0, cur0 = 0, cur1 = 0, cur2 = 0;
+#define FETCH(slot) do { const uint32_t* q_ = bcol + (size_t)(slot) * bstride; pre0 = __ldg(q_); pre1 = __ldg(q_ + bstride); pre2 = __ldg(q_ + 2 * bstride); } while (0)
+#define ADVANCE(op) do { cur0 = pre0; cur1 = pre1; cur2 = pre2; if ((op).next_dslot >= 0) FETCH((op).next_dslot); } while (0)
+    if (sjob.first_dslot >= 0) FETCH(sjob.first_dslot);
     for (int i = 0; i < nops; ++i) {
         if ((i % QSB_EXEC_CHUNK) == 0) {   // refill: the whole block copies the next chunk of ops (coalesced 16-byte loads)
             __syncthreads();
@@ -86,7 +93,8 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
         case TOP_SELECT:
             if (on) {
                 uint32_t m[5];
-                const uint32_t b0 = DBITS(op.dslot), b1 = DBITS(op.dslot + 1), b2 = DBITS(op.dslot + 2);   // bit planes of the selected index
+                ADVANCE(op);
+                const uint32_t b0 = cur0, b1 = cur1, b2 = cur2;   // bit planes of the selected index
                 for (int j = 0; j < 5; ++j) m[j] = ((j & 1) ? b0 : ~b0) & ((j & 2) ? b1 : ~b1) & ((j & 4) ? b2 : ~b2);
                 int planes = op.n * (4 * op.n + 2);
                 for (int p = 0; p < planes; ++p) {
@@ -102,7 +110,8 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
         case TOP_SELECT_CONST:
             if (on) {
                 uint32_t m[5];
-                const uint32_t b0 = DBITS(op.dslot), b1 = DBITS(op.dslot + 1), b2 = DBITS(op.dslot + 2);
+                ADVANCE(op);
+                const uint32_t b0 = cur0, b1 = cur1, b2 = cur2;
                 for (int j = 0; j < 5; ++j) m[j] = ((j & 1) ? b0 : ~b0) & ((j & 2) ? b1 : ~b1) & ((j & 4) ? b2 : ~b2);
                 const uint8_t* tab = sjob.aux + op.obs;
                 const int planes = op.n * (4 * op.n + 2);
@@ -123,14 +132,16 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
             break;
         case TOP_NOISE:
             if (on) {
-                const uint32_t fx = DBITS(op.dslot), fz = DBITS(op.dslot + 1);
+                ADVANCE(op);
+                const uint32_t fx = cur0, fz = cur1;
                 N_SWITCH(op.n, big_noise(PL(op.s[0]), W, op.n, op.q[0], fx, fz), tab_noise_apply(PL(op.s[0]), W, w, N, op.q[0], fx, fz))
             }
             break;
         case TOP_MEASURE:
             if (on) {
                 uint32_t rnd;
-                uint32_t outcome = 0; const uint32_t rb = DBITS(op.dslot);
+                ADVANCE(op);
+                uint32_t outcome = 0; const uint32_t rb = cur0;
                 N_SWITCH(op.n, outcome = big_measure(PL(op.s[1]), PL(op.s[0]), W, op.n, op.q[0], op.iv[0], op.iv[1], rb, &rnd), outcome = tab_measure_bits(PL(op.s[1]), PL(op.s[0]), W, w, N, op.q[0], op.iv[0], op.iv[1], rb, &rnd))
                 uint32_t al = PL(op.al[1])[w];
                 PL(op.m[0])[w] = outcome & al;
@@ -204,7 +215,8 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
             break;
         case TOP_MASK_RANDOM:
             if (on) {
-                PL(op.m[0])[w] = (plane_t)(DBITS(op.dslot) & validw);
+                ADVANCE(op);
+                PL(op.m[0])[w] = (plane_t)(cur0 & validw);
             }
             break;
         case TOP_KILL:
@@ -227,7 +239,8 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
         }
     }
 #undef PL
-#undef DBITS
+#undef FETCH
+#undef ADVANCE
 #undef LANE_ID
 }
 

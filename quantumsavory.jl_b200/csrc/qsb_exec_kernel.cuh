@@ -17,6 +17,7 @@ struct ExecOp {
     int16_t s[6], al[6], m[3];
     int16_t pad;
     int32_t obs, dslot;
+    int32_t next_dslot;       // first decision slot of the NEXT stochastic op (-1: none): its words are fetched one stochastic op ahead
     double* stats;
     double* per_traj;         // TOP_EXPECT: per-trajectory row; TOP_RETIRE: int32 code row (one entry per lane of the context)
 };
@@ -29,16 +30,22 @@ struct ExecJob {
     const TabObsArgs* obs;
     const uint8_t* aux;
     const void* specs;        // DrawSpec[nspecs] (qsb_exec.cu)
+    const void* items;        // DrawItem[nitems]: the specs grouped by Philox block (two draws per block), the draw pass's work list
+    int nitems, pad_items;
     const uint32_t* lanes;    // lane index (trajectory slot of the context) of each of the job's `count` trajectories; nullptr: identity
-    uint32_t* bits;           // decision words of every stochastic op, [word][slot_stride] (a word = 32 trajectories of the job)
+    uint32_t* bits;           // decision words of every stochastic op, [slot][wstride] (a word = 32 trajectories of the job): slot-major,
+                              // so the 32 threads of an executor warp read one 128-byte line per slot
     uint32_t* arena;          // global-memory arena [planes][words] (programs whose tile does not fit in shared memory), else nullptr
-    int nops, nspecs, slot_stride, planes;
+    int nops, nspecs, nslots, planes;
+    uint32_t wstride;         // words per slot row (job words rounded up to 8: rows start on a 32-byte sector)
+    int32_t first_dslot;      // decision slot of the first stochastic op (-1: none)
     uint32_t count, words;    // trajectories of the job, ceil(count / 32)
     uint32_t block0_exec, block0_draw;   // first block of the job in the executor grid / in the draw grid
 };
 struct WaveArgs {
     const ExecJob* jobs; int njobs;
     uint64_t seed, traj0, draw_base;   // global trajectory id of lane index 0, offset of every draw id
+    uint32_t rk[20];                   // Philox round keys (k0, k1 of rounds 0..9) of `seed`: constant-bank operands of the draw pass
     int tile_stride;                   // shared-memory executor: words per thread of the [thread][plane] tile (odd: conflict-free banks)
 };
 

@@ -77,6 +77,14 @@ def test_program_matches_per_op_path(ntraj):
     prog.run(traj_shift=12345 * 32); ctx.sync()
     assert torch.equal(p_shift, p_prog) and torch.equal(s_shift.t[:, :3], s_prog.t[:, :3])
     assert not torch.equal(p_shift, p_direct)
+    # draw_base offsets every draw id: equal to the per-op path whose host counter starts there.  An odd offset changes
+    # which draws share a Philox block (the draw pass then runs its per-spec kernel instead of the block-item list).
+    for base in (6, 7):
+        ctx._draw = base
+        _, s_off, p_off = run(ctx, False)
+        prog.run(draw_base=base); ctx.sync()
+        assert torch.equal(p_off, p_prog) and torch.equal(s_off.t[:, :3], s_prog.t[:, :3]), base
+        assert not torch.equal(p_off, p_direct)
     prog.free(); ctx.close(); ctx2.close()
 
 
