@@ -651,7 +651,23 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     if (rc == QSB_OK) { cudaError_t e = cudaStreamSynchronize(ctx->stream); if (e != cudaSuccess) rc = QSB_ERR_CUDA; }  // host vectors die below
     // launch shape of the full-ensemble replay (reported by qsb_program_info; subsets and waves are shaped at run time)
     const uint32_t full_words = (uint32_t)ctx->nwords;
-    const int t = qsb_exec_shape(ctx, &full_words, 1, P->planes, nullptr);
+    long shape_blocks = 0;
+    int t = qsb_exec_shape(ctx, &full_words, 1, P->planes, &shape_blocks);
+    // Shared memory or global memory for the arena?  The shared-memory executor is latency bound: a block runs for (ops x latency of
+    // an op body) whatever its width, so its run time is (waves x that), and the waves follow from how many word columns fit in an
+    // SM's shared memory.  When the ensemble needs many waves (repeatergrid: 1341 planes -> 42 columns per SM -> 50 waves for 10^7
+    // lanes) the same kernel over a plane-major arena in global memory wins: every word is a thread, 48 warps per SM hide the L2
+    // latency of the plane accesses, and the traffic is what the per-op path would move anyway (measured: 270 -> 93 ms).
+    if (t) {
+        int sm_smem = 0, sms = 1;
+        cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+        long resident = sm_smem / ((long)qsb_exec_stride(P->planes) * t * (long)sizeof(plane_t) + 4096);
+        if (resident < 1) resident = 1;
+        const double waves = (double)shape_blocks / ((double)sms * (double)resident);
+        const char* g = getenv("QSB_EXEC_GLOBAL");          // tuning aid: 1 forces the global-memory arena, 0 the shared-memory tile
+        if (g ? atoi(g) != 0 : waves > 4.0) t = 0;
+    }
     if (t) { P->threads = t; P->smem_bytes = qsb_exec_stride(P->planes) * t * (int)sizeof(plane_t); P->arena = nullptr; }
     else {
         P->threads = 128; P->smem_bytes = 0;
@@ -687,7 +703,6 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
         if (in[j].count < 0 || in[j].count > ctx->ntraj) QSB_FAIL(QSB_ERR_BAD_ARG, "job %d: %lld lanes requested from an ensemble of %lld", j, (long long)in[j].count, (long long)ctx->ntraj);
         if (in[j].P->dprog && (n > 1 || in[j].lanes || in[j].count != ctx->ntraj || (flags & QSB_RUN_KEEP_STATS)))
             QSB_FAIL(QSB_ERR_UNSUPPORTED, "dense programs run on the whole ensemble, one program per launch");
-        if (in[j].P->arena && n > 1) QSB_FAIL(QSB_ERR_UNSUPPORTED, "a program whose arena lives in global memory cannot share a launch");
     }
     if (!(flags & QSB_RUN_KEEP_STATS)) {
         for (int j = 0; j < n; ++j) {
@@ -717,11 +732,11 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
     }
     QSB_TRY(wave_buffer(ctx, (void**)&ctx->wave_bits, &ctx->wave_bits_bytes, (bits_words + 32) * sizeof(uint32_t)));
     QSB_TRY(wave_buffer(ctx, &ctx->wave_jobs, &ctx->wave_jobs_bytes, (size_t)n * sizeof(ExecJob)));
-    const bool global_arena = in[0].P->arena != nullptr;
+    const bool global_arena = n == 1 && in[0].P->arena != nullptr;   // several jobs per launch always take the shared-memory tile
     long blocks = 0;
     int threads;
     if (global_arena) { threads = 128; blocks = (words[0] + 127) / 128; }
-    else if (n == 1 && !in[0].lanes && in[0].count == ctx->ntraj) { threads = in[0].P->threads; blocks = ((long)words[0] + threads - 1) / threads; }
+    else if (n == 1 && !in[0].lanes && in[0].count == ctx->ntraj && !in[0].P->arena) { threads = in[0].P->threads; blocks = ((long)words[0] + threads - 1) / threads; }
     else threads = qsb_exec_shape(ctx, words.data(), n, planes, &blocks);
     if (!threads) QSB_FAIL(QSB_ERR_UNSUPPORTED, "a program of this launch does not fit in shared memory");
     size_t boff = 0;

@@ -3,6 +3,9 @@
 #ifndef QSB_EXEC_T
 #error "compile with -DQSB_EXEC_T=1 (arena tile in shared memory) or 0 (arena in global memory)"
 #endif
+#ifndef QSB_EXEC_G_MINB
+#define QSB_EXEC_G_MINB 6   // resident 128-thread blocks per SM the global-arena executor is compiled for (register cap 80)
+#endif
 
 // The tableau functions are force-inlined with a LITERAL qubit count so that their loops unroll and their
 // per-row scratch arrays live in registers (a run-time n keeps them in local memory: 2.2 KB of stack per thread).
@@ -27,7 +30,7 @@ static __device__ __noinline__ void big_expect(plane_t* p, size_t W, int n, cons
 // One thread owns one 32-trajectory word column of every plane of its job; nothing is exchanged between threads, so
 // consecutive ops need no barrier.  `live` holds the lanes that still belong to the job's cohort (TOP_RETIRE).
 template <int T>
-__global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
+__global__ void __launch_bounds__(T == 1 ? 256 : 128, T == 1 ? 1 : QSB_EXEC_G_MINB) k_tab_exec(WaveArgs a) {
     extern __shared__ plane_t tile[];
     __shared__ ExecJob sjob;
     __shared__ __align__(16) ExecOp sops[QSB_EXEC_CHUNK];   // filled with 16-byte copies
@@ -45,7 +48,8 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128) k_tab_exec(WaveArgs a) {
     // T == 1: the tile is [thread][tile_stride] -- a thread's planes are CONTIGUOUS (plane k at col[k]), so plane offsets fold
     // into the immediate field of LDS/STS, distinct planes are provably distinct addresses (loads may be hoisted above stores:
     // instruction-level parallelism inside an op body) and no address multiply is needed; tile_stride is odd, so the 32
-    // threads of a warp hit 32 different banks.  T == 0: plane-major global arena, plane k at col[k * words].
+    // threads of a warp hit 32 different banks.  T == 0: plane-major global arena, plane k at col[k * words] (a warp reads one
+    // 128-byte line per plane; the [word][plane] layout was measured 2.8x slower there: 32 lines per request thrash the L1).
     plane_t* const col = T ? tile + (size_t)threadIdx.x * (size_t)a.tile_stride : sjob.arena + (on ? wg : 0);
     const size_t W = T ? (size_t)1 : (size_t)sjob.words;
     const size_t w = 0;

@@ -157,14 +157,17 @@ def test_headline_dense_program_on_the_full_firstgenrepeater_dm_schedule():
     prog.free(); ctx.close()
 
 
-def test_repeatergrid_program_at_the_benchmarked_shape():
-    """bench.py's repeatergrid config: 1341 planes -> 42-thread executor blocks.  Statistics rows of the program vs per-op."""
+@pytest.mark.parametrize("waves", [2, 6])
+def test_repeatergrid_program_at_the_benchmarked_shape(waves):
+    """bench.py's repeatergrid config: 1341 planes -> 42-thread executor blocks in shared memory; past 4 waves of them the same
+    executor runs over a plane-major arena in global memory (the shape bench.py times at 10^7 lanes).  Statistics rows of the
+    program vs per-op, both placements."""
     import torch
     from qsb200.backend import BatchContext, CudaBatchRepr
     from qsb200.registers import observable_options
     from qsb200.sharding import StatsBuffer
     b = _bench()
-    ntraj = 2 * 148 * 42 * 32 - 5         # two whole waves of 148 blocks x 42 threads x 32 lanes, ragged last word
+    ntraj = waves * 148 * 42 * 32 - 5     # whole waves of 148 blocks x 42 threads x 32 lanes, ragged last word
     ctx = BatchContext(ntraj, seed=b.SEED)
 
     def one(mode):
@@ -187,7 +190,8 @@ def test_repeatergrid_program_at_the_benchmarked_shape():
 
     prog, s_prog, keys, log, nobs = one("program")
     info = prog.info()
-    assert info["threads"] == 42 and info["planes"] > 1000 and not info["global_arena"], info   # bench.py's shape at 10^7
+    assert info["planes"] > 1000 and bool(info["global_arena"]) == (waves > 4), info
+    assert info["global_arena"] or info["threads"] == 42, info
     prog.run(); ctx.sync()
     _, s_op, keys2, log2, nobs2 = one("per_op")
     assert keys2 == keys and log2 == log and nobs2 == nobs > 0
