@@ -357,7 +357,7 @@ static int qsb_exec_shape(const qsb_ctx* ctx, const uint32_t* words, int njobs, 
     cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device);
     cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-    const size_t per_thread = (size_t)qsb_exec_stride(planes) * sizeof(plane_t), fixed = 1024 + QSB_EXEC_CHUNK * sizeof(ExecOp) + sizeof(ExecJob);
+    const size_t per_thread = (size_t)qsb_exec_stride(planes) * sizeof(plane_t), fixed = 1024 + 2 * QSB_EXEC_CHUNK * sizeof(ExecOp) + sizeof(ExecJob);
     if (per_thread * 32 > (size_t)dev_smem) return 0;
     auto blocks_of = [&](int t) { long b = 0; for (int j = 0; j < njobs; ++j) b += ((long)words[j] + t - 1) / t; return b; };
     const char* force_t = getenv("QSB_EXEC_THREADS");   // tuning aid: pin the block size

@@ -1,5 +1,6 @@
 // qsb_exec_inst.cu -- one instantiation of the fused executor kernel per compilation (-DQSB_EXEC_T=0|1).
 #include "qsb_exec_kernel.cuh"
+#include <cuda_pipeline.h>
 #ifndef QSB_EXEC_T
 #error "compile with -DQSB_EXEC_T=1 (arena tile in shared memory) or 0 (arena in global memory)"
 #endif
@@ -33,7 +34,7 @@ template <int T>
 __global__ void __launch_bounds__(T == 1 ? 256 : 128, T == 1 ? 1 : QSB_EXEC_G_MINB) k_tab_exec(WaveArgs a) {
     extern __shared__ plane_t tile[];
     __shared__ ExecJob sjob;
-    __shared__ __align__(16) ExecOp sops[QSB_EXEC_CHUNK];   // filled with 16-byte copies
+    __shared__ __align__(16) ExecOp sops[2][QSB_EXEC_CHUNK];   // double buffered: chunk c + 1 arrives (cp.async) while chunk c executes
     if (threadIdx.x == 0) {   // the job of this block: largest block0_exec <= blockIdx.x
         int lo = 0, hi = a.njobs - 1;
         while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (a.jobs[mid].block0_exec <= blockIdx.x) lo = mid; else hi = mid - 1; }
@@ -68,15 +69,21 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128, T == 1 ? 1 : QSB_EXEC_G_MI
 #define ADVANCE(op) do { cur0 = pre0; cur1 = pre1; cur2 = pre2; if ((op).next_dslot >= 0) FETCH((op).next_dslot); } while (0)
     if (sjob.first_dslot >= 0) FETCH(sjob.first_dslot);
     for (int i = 0; i < nops; ++i) {
-        if ((i % QSB_EXEC_CHUNK) == 0) {   // refill: the whole block copies the next chunk of ops (coalesced 16-byte loads)
-            __syncthreads();
-            const int nchunk = min(QSB_EXEC_CHUNK, nops - i);
-            const uint4* src = reinterpret_cast<const uint4*>(ops + i);
-            uint4* dst = reinterpret_cast<uint4*>(sops);
-            for (int k = threadIdx.x; k < nchunk * (int)(sizeof(ExecOp) / 16); k += blockDim.x) dst[k] = __ldg(src + k);
-            __syncthreads();
+        if ((i % QSB_EXEC_CHUNK) == 0) {   // chunk boundary: the chunk was requested one chunk ago (the first one just below); request the next
+            const int c = i / QSB_EXEC_CHUNK;
+            auto request = [&](int first, int buf) {
+                const int nchunk = min(QSB_EXEC_CHUNK, nops - first);
+                const uint4* src = reinterpret_cast<const uint4*>(ops + first);
+                uint4* dst = reinterpret_cast<uint4*>(sops[buf]);
+                for (int k = threadIdx.x; k < nchunk * (int)(sizeof(ExecOp) / 16); k += blockDim.x) __pipeline_memcpy_async(dst + k, src + k, 16);
+                __pipeline_commit();
+            };
+            if (i == 0) request(0, 0);
+            __pipeline_wait_prior(0);
+            __syncthreads();               // chunk c is complete for every thread, and nobody still reads the buffer chunk c + 1 goes to
+            if (i + QSB_EXEC_CHUNK < nops) request(i + QSB_EXEC_CHUNK, (c + 1) & 1);
         }
-        const ExecOp& op = sops[i % QSB_EXEC_CHUNK];
+        const ExecOp& op = sops[(i / QSB_EXEC_CHUNK) & 1][i % QSB_EXEC_CHUNK];
         switch (op.type) {
         case TOP_INIT:
             if (on) { N_SWITCH(op.n, big_init(PL(op.s[0]), W, op.n, op.iv[0]), tab_init_word(PL(op.s[0]), W, w, N, op.iv[0])) PL(op.al[0])[w] = validw; }

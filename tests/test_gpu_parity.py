@@ -347,3 +347,40 @@ def test_tma_staged_gate_equals_register_path():
     assert np.array_equal(got["0"], got["2"]) and np.array_equal(got["0"], got["3"])
     assert abs(np.trace(got["0"][0].reshape(32, 32, order="F")) - 1) < 1e-12
     ctx.close()
+
+
+def test_dense_observable_on_clifford_states_equals_the_dense_path():
+    """observable(::MixedDestabilizer, idx, ::Operator) (src/backends/clifford/express.jl:22-46): here a Pauli-basis expansion of
+    the operator, so it must agree with the QuantumOptics path on the same (also mixed) states, trajectory by trajectory."""
+    import warnings
+    from qsb200 import ops
+    from qsb200.backend import BatchContext, CudaBatchRepr
+    from qsb200.registers import Register, apply, initialize, observable, project_traceout
+    rng = np.random.default_rng(5)
+    a = rng.normal(size=(4, 4)) + 1j * rng.normal(size=(4, 4))
+    herm, general = (a + a.conj().T) / 2, a
+    one = rng.normal(size=(2, 2)) + 1j * rng.normal(size=(2, 2))
+    ctx = BatchContext(70, seed=77)
+    res = {}
+    for f in ("clifford", "qo"):
+        ctx._draw = 0
+        reg = Register(4, CudaBatchRepr(ctx, f))
+        initialize(reg[1:3], ops.StabilizerState("XXX ZZI IZZ"))
+        initialize(reg[4], ops.MixedState(1))                       # rank-deficient: the reference would throw, the expansion does not care
+        apply((reg[3], reg[4]), ops.CNOT)
+        apply(reg[2], ops.H)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            vals = [observable((reg[1], reg[3]), herm, per_trajectory=True).values(), observable((reg[4], reg[2]), general, per_trajectory=True).values(),
+                    observable(reg[2], one, per_trajectory=True).values()]
+        m = project_traceout(reg[1], ops.X)                          # outcomes differ between trajectories from here on
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            v = observable((reg[2], reg[3]), herm, per_trajectory=True)
+        vals.append(v.values())
+        res[f] = (vals, m.numpy(), v.mean, v.var)
+    for x, y in zip(res["clifford"][0], res["qo"][0]):
+        assert np.abs(x - y).max() < 1e-12
+    assert (res["clifford"][1] == res["qo"][1]).all()
+    assert abs(res["clifford"][2] - res["qo"][2]) < 1e-12 and abs(res["clifford"][3] - res["qo"][3]) < 1e-12
+    ctx.close()
