@@ -629,6 +629,11 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
         for (int j = 0; j < 6; ++j) { x.s[j] = (int16_t)o.s[j]; x.al[j] = (int16_t)o.al[j]; }
         for (int j = 0; j < 3; ++j) x.m[j] = (int16_t)o.m[j];
         x.obs = o.obs; x.dslot = o.dslot; x.next_dslot = (int32_t)o.lut; x.stats = o.stats; x.per_traj = o.per_traj;
+        if (o.type == TOP_EXPECT) {   // single-Pauli observables carry their arguments in the record
+            const TabObsArgs& oa = R->obs[o.obs];
+            x.k = oa.nelem == 1 ? 1 : 0;
+            if (x.k) { x.u[0] = oa.px[0]; x.u[1] = oa.pz[0]; x.iv[0] = oa.sign[0]; }
+        }
     }
     if (!xops.empty() && rc == QSB_OK) {
         if (cudaMallocHost((void**)&P->h_ops, xops.size() * sizeof(ExecOp)) != cudaSuccess) { cudaGetLastError(); qsb_set_error("pinned allocation of the op list failed"); rc = QSB_ERR_OOM; }

@@ -22,6 +22,7 @@ static __device__ __noinline__ void big_noise(plane_t* p, size_t W, int n, int q
 static __device__ __noinline__ uint32_t big_measure(plane_t* in, plane_t* out, size_t W, int n, int q, int tx, int tz, uint32_t rb, uint32_t* rnd) { return tab_measure_bits(in, out, W, 0, n, q, tx, tz, rb, rnd); }
 static __device__ __noinline__ void big_ptrace(plane_t* in, plane_t* out, size_t W, int n, int q) { tab_ptrace_word(in, out, W, 0, n, q); }
 static __device__ __noinline__ void big_force(plane_t* p, size_t W, int n, uint32_t px, uint32_t pz, int sign) { tab_force_word(p, W, 0, n, px, pz, sign); }
+static __device__ __noinline__ void big_expect1(plane_t* p, size_t W, int n, uint32_t px, uint32_t pz, int sign, uint32_t* plus, uint32_t* minus) { tab_expect_pauli(p, W, 0, n, px, pz, sign, plus, minus); }
 static __device__ __noinline__ void big_expect(plane_t* p, size_t W, int n, const TabObsArgs& a, uint32_t* cnt, uint32_t* cntm) { tab_expect_word_n(p, W, 0, n, a, cnt, cntm); }
 
 // T == 1: the arena is a [blockDim.x][tile_stride] tile of shared memory.  The block size is a RUN-TIME value (any thread count
@@ -170,10 +171,17 @@ __global__ void __launch_bounds__(T == 1 ? 256 : 128, T == 1 ? 1 : QSB_EXEC_G_MI
             int n_alive = 0, num = 0, num2 = 0;
             int nelem = 1;
             if (on) {
-                const TabObsArgs& o = sjob.obs[op.obs];
-                nelem = o.nelem;
                 uint32_t cnt[8], cntm[8];
-                N_SWITCH(op.n, big_expect(PL(op.s[0]), W, op.n, o, cnt, cntm), tab_expect_word_n(PL(op.s[0]), W, w, N, o, cnt, cntm))
+                if (op.k == 1) {     // a single Pauli: px, pz and the sign travel in the op record (no loads from the argument table)
+#pragma unroll
+                    for (int b = 1; b < 8; ++b) { cnt[b] = 0; cntm[b] = 0; }
+                    N_SWITCH(op.n, big_expect1(PL(op.s[0]), W, op.n, op.u[0], op.u[1], op.iv[0], &cnt[0], &cntm[0]),
+                             tab_expect_pauli(PL(op.s[0]), W, w, N, op.u[0], op.u[1], op.iv[0], &cnt[0], &cntm[0]))
+                } else {
+                    const TabObsArgs& o = sjob.obs[op.obs];
+                    nelem = o.nelem;
+                    N_SWITCH(op.n, big_expect(PL(op.s[0]), W, op.n, o, cnt, cntm), tab_expect_word_n(PL(op.s[0]), W, w, N, o, cnt, cntm))
+                }
                 const uint32_t al = PL(op.al[0])[w] & live;   // retired lanes left this cohort: they are tallied where they continue
                 n_alive = __popc(al);
                 if (nelem == 1 && !op.per_traj) {   // a single Pauli: each lane holds -1, 0 or +1

@@ -21,7 +21,7 @@ struct ExecOp {
     double* stats;
     double* per_traj;         // TOP_EXPECT: per-trajectory row; TOP_RETIRE: int32 code row (one entry per lane of the context)
 };
-#define QSB_EXEC_CHUNK 32   // ops staged per shared-memory refill
+#define QSB_EXEC_CHUNK 32   // ops per staged chunk, two buffers (64-op chunks save barriers at level 0 but their 10 KB per block cost a wave at the small-block tree levels)
 
 // One (program, lane subset) pair of a launch.  A launch ("wave") executes any number of jobs: block b belongs to the job
 // with the largest block0 <= b.  The full-ensemble replay is the one-job case with lanes == nullptr.

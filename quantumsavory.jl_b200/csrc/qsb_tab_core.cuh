@@ -535,5 +535,20 @@ QSB_HD void tab_expect_word_n(plane_t* p, size_t W, size_t w, int n, const TabOb
         for (int b = 0; b < 8 && carry; ++b) { uint32_t t = cntm[b] & carry; cntm[b] ^= carry; carry = t; }
     }
 }
+// a single Pauli (the common observable): lanes with <P> = +1 / -1; everything the generic routine reads from its argument
+// table comes in registers here (the fused executor embeds px, pz and the sign in the op record)
+QSB_HD void tab_expect_pauli(plane_t* p, size_t W, size_t w, int n, uint32_t px, uint32_t pz, int sign, uint32_t* plus, uint32_t* minus) {
+    TabView v = make_view(p, W, w, n);
+    uint32_t nonzero, neg;
+    if ((px | pz) == 0) { nonzero = QSB_FULL; neg = sign ? QSB_FULL : 0u; }
+    else {
+        Analysis A;
+        uint32_t pivD[MAXN];
+        analyze(v, px, pz, A, pivD);
+        nonzero = ~A.found & QSB_FULL;
+        neg = determined_sign(v, A, nonzero) ^ (sign ? nonzero : 0u);
+    }
+    *plus = nonzero & ~neg; *minus = nonzero & neg;
+}
 }  // namespace QSB_CORE_NS
 using namespace QSB_CORE_NS;

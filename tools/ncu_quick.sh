@@ -6,6 +6,7 @@ $M > gpurun_out/${tag}_plain.json 2>/dev/null || exit 1
 ncu --set full --clock-control none --import-source on -k regex:'k_tab_exec|k_draw' -c 2 -o gpurun_out/${tag} $M > /dev/null 2>&1
 ncu -i gpurun_out/${tag}.ncu-rep --page raw --csv > gpurun_out/${tag}_raw.csv 2>/dev/null
 ncu -i gpurun_out/${tag}.ncu-rep --page source --csv > gpurun_out/${tag}_source.csv 2>/dev/null
+ncu -i gpurun_out/${tag}.ncu-rep --page source --csv --print-source cuda -k regex:k_tab_exec > gpurun_out/${tag}_lines.csv 2>/dev/null
 rm -f gpurun_out/${tag}.ncu-rep
 gzip -f gpurun_out/${tag}_source.csv
 python tools/ncu_summary.py gpurun_out/${tag}_raw.csv
