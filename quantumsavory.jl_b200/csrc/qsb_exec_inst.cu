@@ -10,12 +10,21 @@
 
 // The tableau functions are force-inlined with a LITERAL qubit count so that their loops unroll and their
 // per-row scratch arrays live in registers (a run-time n keeps them in local memory: 2.2 KB of stack per thread).
-// States of more than 5 qubits take a NOINLINE fallback with a run-time n (its arrays live in local memory); keeping it out of
+// States of more than 4 qubits take a NOINLINE fallback with a run-time n (its arrays live in local memory); keeping it out of
 // line lets the compiler allocate registers for the literal cases alone (inline it cost 2.2 KB of stack frame and capped the
 // kernel at 64 registers with spills).
 #define N_CASE(K, ...) case K: { constexpr int N = K; __VA_ARGS__; } break;
+// Literal cases stop at 4 qubits (the largest state of the BASELINE workloads): the kernel's code size grows with the square of the
+// literal n, and with 1-2 warps per scheduler instruction-fetch stalls are not hidden (ncu: 4.8 no-instruction stalls per issue on the
+// one-warp blocks of tree level 3, 13 on the global-arena executor, with a fifth literal case that no workload used).
+// (The global-arena instantiation keeps its fifth case: without it ptxas spills at the 80-register cap and the grid ran 13 % slower.)
+#if QSB_EXEC_T
+#define N_CASE5(...)
+#else
+#define N_CASE5(...) N_CASE(5, __VA_ARGS__)
+#endif
 #define N_SWITCH(NV, FALLBACK, ...) switch (NV) { N_CASE(1, __VA_ARGS__) N_CASE(2, __VA_ARGS__) N_CASE(3, __VA_ARGS__) N_CASE(4, __VA_ARGS__) \
-                                        N_CASE(5, __VA_ARGS__) default: { FALLBACK; } break; }
+                                        N_CASE5(__VA_ARGS__) default: { FALLBACK; } break; }
 static __device__ __noinline__ void big_init(plane_t* p, size_t W, int n, int active) { tab_init_word(p, W, 0, n, active); }
 static __device__ __noinline__ void big_gate(plane_t* p, size_t W, int n, int k, int q0, int q1, const uint8_t* om, uint32_t anf, uint32_t m) { tab_gate_anf(p, W, 0, n, k, q0, q1, om, anf, m); }
 static __device__ __noinline__ void big_noise(plane_t* p, size_t W, int n, int q, uint32_t fx, uint32_t fz) { tab_noise_apply(p, W, 0, n, q, fx, fz); }
