@@ -227,6 +227,10 @@ int qsb_program_info(const qsb_program* prog, int64_t info[8]);
 /* SURVEY.md 8d table bytes of the recorded ops summed over trajectories: the algorithmic traffic the SAME op list
  * accounts when every op is its own launch (the numerator of roofline.achieved for the fused launch). */
 int qsb_program_table_bytes(const qsb_program* prog, uint64_t* bytes);
+/* verification aid (host-visible): the raw records of a tableau program as the executor reads them -- what = 0 op records, 1 draw
+ * specs, 2 observable tables, 3 constant tables, 4 statistics row pointers, 5 int32 {planes, slots, ops, specs, obs, aux, rows,
+ * first slot}; layouts in csrc/qsb_exec_kernel.cuh, not a stable ABI.  bench.py's bit-sliced CPU baseline replays them. */
+int qsb_program_export(const qsb_program* prog, int what, void* buf, size_t buflen, size_t* needed);
 int qsb_program_free(qsb_program* prog);
 
 #ifdef __cplusplus

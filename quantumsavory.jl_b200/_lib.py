@@ -112,6 +112,7 @@ def _declare(L):
         "qsb_program_info": (C.c_int, [vp, i64p]),
         "qsb_program_upload": (C.c_int, [vp, i64p]),
         "qsb_program_table_bytes": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
+        "qsb_program_export": (C.c_int, [vp, C.c_int, vp, C.c_size_t, C.POINTER(C.c_size_t)]),
         "qsb_program_free": (C.c_int, [vp]),
         "qsb_state_alive": (C.c_int, [vp, vpp]),
         "qsb_state_kill": (C.c_int, [vp, vp]),

@@ -138,6 +138,19 @@ class Program:
         d["table_bytes"] = b.value
         return d
 
+    def export(self):
+        """Raw records of a tableau program (qsb_program_export): {'ops','specs','obs','aux','stats','meta'} as bytes / int arrays."""
+        out = {}
+        for what, name in enumerate(("ops", "specs", "obs", "aux", "stats", "meta")):
+            need = C.c_size_t(0)
+            check(self.ctx.L.qsb_program_export(self.p, what, None, 0, C.byref(need)))
+            buf = (C.c_uint8 * max(1, need.value))()
+            check(self.ctx.L.qsb_program_export(self.p, what, buf, need.value, C.byref(need)))
+            out[name] = bytes(buf[: need.value])
+        out["meta"] = np.frombuffer(out["meta"], np.int32)
+        out["stats"] = np.frombuffer(out["stats"], np.uint64)
+        return out
+
     def free(self):
         if self.p and self.ctx.p:
             self.ctx.L.qsb_program_free(self.p)

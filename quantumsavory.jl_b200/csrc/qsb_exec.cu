@@ -20,18 +20,6 @@
 #include "qsb_exec_kernel.cuh"
 #include "qsb_dexec.cuh"
 
-// one stochastic op of the program as the draw pass sees it
-struct DrawSpec {
-    uint64_t draw;
-    int type, np, slot;        // type: TOP_NOISE / TOP_SELECT / TOP_MEASURE / TOP_MASK_RANDOM
-    uint32_t thr_hi_any;       // noise: high word of ((thr_any + 1) << 11) -- hi32(draw bits) < thr_hi_any on every lane proves "no error in this word"
-    // the comparisons of the per-op kernels (u = k / 2^53 against a double c) restated EXACTLY on the 53-bit integer k:
-    //   u > c  <=>  k > floor(c * 2^53)        u < c  <=>  k < ceil(c * 2^53)        (c * 2^53 is exact in a double)
-    uint64_t thr[5];
-    uint64_t thr_any;          // noise: the lowest threshold -- k <= thr_any on every lane means "no error anywhere in this word"
-    uint8_t code[4];           // noise: 2-bit decision (bit 0: X component, bit 1: Z component) of branch j
-    int pad2;
-};
 #define QSB_DRAW_CHUNK 64      // specs staged per shared-memory refill of the draw pass
 // The draw pass's work list: one item per Philox block (= two consecutive draw ids), so a block is computed once and its two
 // halves are consumed without any "is this block already in registers" test.  32 bytes = two 128-bit shared-memory loads.
@@ -849,6 +837,33 @@ extern "C" int qsb_program_info(const qsb_program* P, int64_t info[8]) {
     info[0] = P->nops; info[1] = P->planes; info[2] = P->nstats; info[3] = P->threads; info[4] = P->smem_bytes; info[5] = P->arena ? 1 : 0;
     if (P->dprog) qsb_dexec_info(P->dprog, info);
     info[2] = P->nstats; info[6] = (int64_t)P->ops_per_run; info[7] = (int64_t)P->draws_per_run;
+    return QSB_OK;
+}
+
+// Raw records of a tableau program as the executor reads them (layouts: csrc/qsb_exec_kernel.cuh -- a verification aid, not a stable
+// ABI): what = 0 ExecOp[], 1 DrawSpec[], 2 TabObsArgs[], 3 aux bytes, 4 statistics row pointers (device addresses, row order),
+// 5 int32 {planes, nslots, nops, nspecs, nobs, naux, nstats, first_dslot}.  *needed receives the size; data is copied when buf holds it.
+// Host-visible.  Used by the bit-sliced CPU replay of bench.py / tests (oracle/qsb_bitsliced.cpp), never by the product.
+extern "C" int qsb_program_export(const qsb_program* P, int what, void* buf, size_t buflen, size_t* needed) {
+    if (!P || !needed) QSB_FAIL(QSB_ERR_BAD_ARG, "null argument");
+    if (P->dprog) QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_program_export covers tableau programs");
+    qsb_use_device(P->ctx);
+    const int32_t meta[8] = {P->planes, P->nslots, P->nops, P->nspecs, P->nobs, P->naux, P->nstats, P->first_dslot};
+    const void* src = nullptr; size_t n = 0; bool dev = true;
+    switch (what) {
+        case 0: src = P->d_ops; n = (size_t)P->nops * sizeof(ExecOp); break;
+        case 1: src = P->d_specs; n = (size_t)P->nspecs * sizeof(DrawSpec); break;
+        case 2: src = P->d_obs; n = (size_t)P->nobs * sizeof(TabObsArgs); break;
+        case 3: src = P->d_aux; n = (size_t)P->naux; break;
+        case 4: src = P->d_stats; n = (size_t)P->nstats * sizeof(double*); break;
+        case 5: src = meta; n = sizeof(meta); dev = false; break;
+        default: QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_program_export: unknown section %d", what);
+    }
+    *needed = n;
+    if (!buf || buflen < n || n == 0) return QSB_OK;
+    if (!dev) { memcpy(buf, src, n); return QSB_OK; }
+    QSB_CUDA(cudaMemcpyAsync(buf, src, n, cudaMemcpyDeviceToHost, P->ctx->stream));
+    QSB_CUDA(cudaStreamSynchronize(P->ctx->stream));
     return QSB_OK;
 }
 

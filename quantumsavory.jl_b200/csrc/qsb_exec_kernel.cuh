@@ -49,6 +49,19 @@ struct WaveArgs {
     int tile_stride;                   // shared-memory executor: words per thread of the [thread][plane] tile (odd: conflict-free banks)
 };
 
+// one stochastic op of the program as the draw pass sees it
+struct DrawSpec {
+    uint64_t draw;
+    int type, np, slot;        // type: TOP_NOISE / TOP_SELECT / TOP_MEASURE / TOP_MASK_RANDOM
+    uint32_t thr_hi_any;       // noise: high word of ((thr_any + 1) << 11) -- hi32(draw bits) < thr_hi_any on every lane proves "no error in this word"
+    // the comparisons of the per-op kernels (u = k / 2^53 against a double c) restated EXACTLY on the 53-bit integer k:
+    //   u > c  <=>  k > floor(c * 2^53)        u < c  <=>  k < ceil(c * 2^53)        (c * 2^53 is exact in a double)
+    uint64_t thr[5];
+    uint64_t thr_any;          // noise: the lowest threshold -- k <= thr_any on every lane means "no error anywhere in this word"
+    uint8_t code[4];           // noise: 2-bit decision (bit 0: X component, bit 1: Z component) of branch j
+    int pad2;
+};
+
 // launchers: [0] arena in global memory (one job per launch), [1] shared-memory tile with a run-time block size
 typedef cudaError_t (*qsb_exec_launch_fn)(const WaveArgs&, unsigned blocks, int threads, int smem_bytes, cudaStream_t stream);
 qsb_exec_launch_fn qsb_exec_launcher(int variant);
