@@ -142,7 +142,7 @@ int qsb_channel(qsb_state* st, int idx, int background, const double params[2], 
  * exp(L t) of the k-qubit block is computed once on the host and applied in one pass (no solver tolerance).
  * DM / KET (promoted with dm(), :21-23): exact.  MCKET: nl == 0 -> exp(-iHt) psi (:31-32); nl > 0 -> one sampled
  * branch of the canonical Kraus form of exp(L t) (an unravelling whose ensemble mean is the master-equation solution,
- * like mcwf :33-34; consumes draw_id; k == 1).  TAB: QSB_ERR_UNSUPPORTED (the reference has no method either). */
+ * like mcwf :33-34; consumes draw_id).  TAB: QSB_ERR_UNSUPPORTED (the reference has no method either). */
 int qsb_evolve(qsb_state* st, const int* idx, int k, const double* H_ri, int nl, const int* l_pos, const double* L_ri,
                double duration, uint64_t draw_id);
 /* project_traceout!(state, stateindex, basis) -> (j, newstate): quantumoptics.jl:47-64 (+ express.jl:7-12

@@ -16,7 +16,8 @@
 //   MCKet with collapse operators (mcwf, noninstant.jl:33-34): one sampled branch of the canonical Kraus form of exp(L t)
 //   (eigenvectors of its Choi matrix).  Like mcwf this is an unravelling of the master equation into normalised pure
 //   states whose ensemble mean is the master-equation solution; individual jump records are not comparable with the
-//   reference's (its draws come from inside the ODE solver's callbacks).  k = 1 only.
+//   reference's (its draws come from inside the ODE solver's callbacks).  k = 1: the sampled-Kraus kernels of uptotime!;
+//   k = 2: k_rdm2_ket (reduced 4x4 density matrix) -> k_mc2_finalize (probabilities psi' K'K psi, draw) -> k_apply_kraus2_sel.
 #include <math.h>
 
 #include <complex>
@@ -59,6 +60,81 @@ __global__ void __launch_bounds__(TPB) k_apply_super(double2* d, int64_t npad, s
 #pragma unroll
             for (int w = 0; w < V; ++w) cfma(acc, sS[v + w * V], x[w]);
             d[elem(v)] = acc;
+        }
+    }
+}
+
+// ---- two-subsystem sampled Kraus branch on a trajectory ket (the mcwf case of a 2-qubit ConstantHamiltonianEvolution) ----------
+// table layout in device memory: E[m] = K_m' K_m (16 complex, column-major 4x4) for m < 16, then K[m] (16 complex each)
+// reduced 4x4 density matrix of the two target qubits, split over the other 2^(n-2) indices: partial[(s*32 + 2 v (+1)) * npad + t]
+__global__ void __launch_bounds__(TPB) k_rdm2_ket(const double2* __restrict__ d, int64_t npad, int q0, int q1, size_t range, int nsplit, double* __restrict__ partial) {
+    int64_t t = blockIdx.x * (int64_t)TPB + threadIdx.x;
+    if (t >= npad) return;
+    const int s = blockIdx.y;
+    const size_t lo = range * s / nsplit, hi = range * (s + 1) / nsplit;
+    const int qa = q0 < q1 ? q0 : q1, qb = q0 < q1 ? q1 : q0;
+    double2 R[16];   // R[a + 4 b] = sum psi_a conj(psi_b), a = bit(q0) | bit(q1) << 1
+#pragma unroll
+    for (int v = 0; v < 16; ++v) R[v] = make_double2(0, 0);
+    for (size_t g = lo; g < hi; ++g) {
+        const size_t base = qsb_insert0(qsb_insert0(g, qa), qb);
+        double2 x[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) x[a] = d[(base | ((size_t)(a & 1) << q0) | ((size_t)(a >> 1) << q1)) * npad + t];
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int a = 0; a < 4; ++a) { const double2 c = cmulc(x[a], x[b]); R[a + 4 * b].x += c.x; R[a + 4 * b].y += c.y; }
+    }
+    const size_t o = (size_t)s * 32 * npad + t;
+#pragma unroll
+    for (int v = 0; v < 16; ++v) { partial[o + (size_t)(2 * v) * npad] = R[v].x; partial[o + (size_t)(2 * v + 1) * npad] = R[v].y; }
+}
+__global__ void k_mc2_finalize(const double* __restrict__ partial, int nsplit, int64_t npad, const double2* __restrict__ tab, int nk,
+                               uint64_t seed, uint64_t traj0, uint64_t draw_id, double* __restrict__ scale, int* __restrict__ sel) {
+    int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (t >= npad) return;
+    double2 R[16];
+    for (int v = 0; v < 16; ++v) {
+        double re = 0, im = 0;
+        for (int s = 0; s < nsplit; ++s) { const size_t o = (size_t)s * 32 * npad + t; re += partial[o + (size_t)(2 * v) * npad]; im += partial[o + (size_t)(2 * v + 1) * npad]; }
+        R[v] = make_double2(re, im);
+    }
+    // P_m = psi' E_m psi = sum_{a,b} E_m[b,a] R[a,b]   (R[a + 4b] = sum psi_a conj(psi_b))
+    double P[16], total = 0;
+    for (int m = 0; m < nk; ++m) {
+        double acc = 0;
+        for (int b = 0; b < 4; ++b) for (int a = 0; a < 4; ++a) { const double2 e = tab[m * 16 + b + 4 * a]; acc += e.x * R[a + 4 * b].x - e.y * R[a + 4 * b].y; }
+        P[m] = acc; total += acc;
+    }
+    const double thr = qsb_draw(seed, traj0 + (uint64_t)t, draw_id) * total;
+    double cum = 0;
+    int choice = nk - 1;
+    for (int m = 0; m < nk; ++m) { cum += P[m]; if (cum > thr) { choice = m; break; } }
+    sel[t] = choice;
+    scale[t] = 1.0 / sqrt(P[choice] > 0 ? P[choice] : 1.0);
+}
+__global__ void __launch_bounds__(TPB) k_apply_kraus2_sel(double2* d, int64_t npad, size_t groups, int q0, int q1, const double2* __restrict__ tab,
+                                                          const double* __restrict__ scale, const int* __restrict__ sel) {
+    int64_t t = blockIdx.x * (int64_t)TPB + threadIdx.x;
+    if (t >= npad) return;
+    const double2* K = tab + 256 + (size_t)sel[t] * 16;   // column-major 4x4: K[r + 4 c]
+    const double sc = scale[t];
+    double2 k[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) k[i] = cscale(K[i], sc);
+    const int qa = q0 < q1 ? q0 : q1, qb = q0 < q1 ? q1 : q0;
+    for (size_t g = blockIdx.y; g < groups; g += gridDim.y) {
+        const size_t base = qsb_insert0(qsb_insert0(g, qa), qb);
+        double2 x[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) x[a] = d[(base | ((size_t)(a & 1) << q0) | ((size_t)(a >> 1) << q1)) * npad + t];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            double2 acc = make_double2(0, 0);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) cfma(acc, k[r + 4 * c], x[c]);
+            d[(base | ((size_t)(r & 1) << q0) | ((size_t)(r >> 1) << q1)) * npad + t] = acc;
         }
     }
 }
@@ -169,7 +245,53 @@ int qsbd_evolve(qsb_state* st, const int* idx, int k, const double* H_ri, int nl
     for (auto& v : M) v *= duration;
     expm(V, M.data(), S.data());
     if (st->kind == QSB_MCKET) {
-        if (k != 1) QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_evolve of a trajectory ket with collapse operators is implemented for one subsystem");
+        if (k == 2) {
+            // Choi matrix of the 2-qubit channel: C[(r,r'),(c,c')] = S[(r,c),(r',c')], indices r + 4 r'; K_m = sqrt(w_m) unvec(v_m)
+            std::vector<cd> C(256), Vv; std::vector<double> w;
+            for (int r = 0; r < 4; ++r) for (int r2 = 0; r2 < 4; ++r2) for (int c = 0; c < 4; ++c) for (int c2 = 0; c2 < 4; ++c2)
+                C[(r + 4 * r2) + 16 * (c + 4 * c2)] = S[(r + 4 * c) + 16 * (r2 + 4 * c2)];
+            for (int i = 0; i < 16; ++i) for (int j = i + 1; j < 16; ++j) { cd h = 0.5 * (C[i + 16 * j] + std::conj(C[j + 16 * i])); C[i + 16 * j] = h; C[j + 16 * i] = std::conj(h); }
+            jacobi_herm(16, C, w, Vv);
+            std::vector<int> order(16);
+            for (int i = 0; i < 16; ++i) order[i] = i;
+            for (int i = 1; i < 16; ++i) for (int j = i; j > 0 && w[order[j]] > w[order[j - 1]]; --j) { int t2 = order[j]; order[j] = order[j - 1]; order[j - 1] = t2; }
+            std::vector<cd> tab(512, cd(0));   // [0,256): E_m = K_m' K_m ; [256,512): K_m
+            int nk = 0;
+            for (int m = 0; m < 16; ++m) {
+                const int e = order[m];
+                if (w[e] < 1e-15) continue;
+                const double sq = sqrt(w[e]);
+                cd* K = tab.data() + 256 + nk * 16; cd* E = tab.data() + nk * 16;
+                for (int i = 0; i < 16; ++i) K[i] = sq * Vv[i + 16 * e];                       // i = r + 4 r'
+                for (int a = 0; a < 4; ++a) for (int b = 0; b < 4; ++b) { cd acc = 0; for (int r = 0; r < 4; ++r) acc += std::conj(K[r + 4 * a]) * K[r + 4 * b]; E[a + 4 * b] = acc; }
+                ++nk;
+            }
+            void* dtab;
+            QSB_TRY(qsb_upload(ctx, tab.data(), tab.size() * sizeof(cd), &dtab));
+            const size_t range = (size_t)1 << (n - 2);
+            size_t want = ((size_t)ctx->sm_count * 2048 + ctx->npad - 1) / ctx->npad;
+            int nsplit = (int)(want < 1 ? 1 : want > range ? range : want > 256 ? 256 : want);
+            QSB_TRY(qsb_ensure_scratch(ctx, ((size_t)nsplit * 32 + 2) * ctx->npad * sizeof(double)));
+            dim3 grid((unsigned)((ctx->npad + TPB - 1) / TPB), nsplit, 1);
+            QSB_PRE(ctx, "k_rdm2_ket");
+            k_rdm2_ket<<<grid, TPB, 0, ctx->stream>>>((const double2*)st->data, ctx->npad, idx[0], idx[1], range, nsplit, ctx->scratch);
+            QSB_LAUNCH_CHECK(ctx);
+            double* scale = ctx->scratch + (size_t)nsplit * 32 * ctx->npad;
+            int* sel = (int*)(scale + ctx->npad);
+            QSB_PRE(ctx, "k_mc2_finalize");
+            k_mc2_finalize<<<(unsigned)((ctx->npad + 127) / 128), 128, 0, ctx->stream>>>(ctx->scratch, nsplit, ctx->npad, (const double2*)dtab, nk, ctx->seed, (uint64_t)ctx->traj_offset, draw_id, scale, sel);
+            QSB_LAUNCH_CHECK(ctx);
+            unsigned gx2 = (unsigned)((ctx->npad + TPB - 1) / TPB);
+            size_t gy2 = ((size_t)ctx->sm_count * 32 + gx2 - 1) / gx2;
+            if (gy2 > range) gy2 = range;
+            if (gy2 < 1) gy2 = 1;
+            if (gy2 > 65535) gy2 = 65535;
+            QSB_PRE(ctx, "k_apply_kraus2_sel");
+            k_apply_kraus2_sel<<<dim3(gx2, (unsigned)gy2), TPB, 0, ctx->stream>>>((double2*)st->data, ctx->npad, range, idx[0], idx[1], (const double2*)dtab, scale, sel);
+            QSB_LAUNCH_CHECK(ctx);
+            qsb_account(ctx, "k_apply_kraus2_sel", (uint64_t)32 * ((uint64_t)1 << n) * ctx->ntraj); ctx->ops += ctx->ntraj; ctx->draws++;
+            return QSB_OK;
+        }
         // Choi matrix C[(r,r'),(c,c')] = S[(r,c),(r',c')] = sum_m vec(K_m) vec(K_m)': K_m = sqrt(w_m) unvec(v_m)
         std::vector<cd> C(16), Vv; std::vector<double> w;
         for (int r = 0; r < 2; ++r) for (int r2 = 0; r2 < 2; ++r2) for (int c = 0; c < 2; ++c) for (int c2 = 0; c2 < 2; ++c2)

@@ -111,3 +111,38 @@ def test_refusals(ctx):
         initialize(r[1], S.X1)
         with pytest.raises(MethodError):
             apply(r[1], ConstantHamiltonianEvolution(ops.Z, 0.1))
+
+
+def test_two_qubit_mcket_evolution_with_collapse_operators():
+    """mcwf of a 2-qubit ConstantHamiltonianEvolution: sampled branch of the canonical Kraus form of the 16x16 propagator
+    (k_rdm2_ket -> k_mc2_finalize -> k_apply_kraus2_sel); the ensemble mean is the master-equation solution, kets stay normalised."""
+    from qsb200 import ops
+    from qsb200 import symbols as S
+    from qsb200.backend import BatchContext, CudaBatchRepr
+    from qsb200.registers import ConstantHamiltonianEvolution, Register, apply, initialize, observable
+    N = 20000
+    c = BatchContext(N, seed=0xE503)
+    H = 0.6 * S.tensor(S.Z, S.Z) + 0.4 * S.tensor(S.X, S.Id) + 0.25 * S.tensor(S.Id, S.Y)
+    bgs = [S.T1T2Noise(1.0, 0.8), S.T2Dephasing(1.5), None]
+    reg = Register(3, CudaBatchRepr(c, "mc"), bgs)
+    initialize(reg[1], S.X1); initialize(reg[2], S.Y1); initialize(reg[3], S.Z1)
+    apply((reg[2], reg[3]), ops.CNOT)                      # a spectator entangled with the second evolving qubit
+    d0 = c._draw
+    _, t_end = apply((reg[1], reg[2]), ConstantHamiltonianEvolution(H, 0.7))
+    assert t_end == 0.7 and c._draw == d0 + 1              # one draw per call
+    psi0 = S.tensor(S.X1, S.CNOT @ S.tensor(S.Y1, S.Z1))
+    lind = [(0, L) for L in S.lindbladop(bgs[0])] + [(1, L) for L in S.lindbladop(bgs[1])]
+    want = exact_master(S.dm(psi0), 3, [0, 1], H, lind, 0.7)
+    for names in ("XII", "ZZI", "IYX", "ZIZ", "YXZ", "IIZ"):
+        P = ops.tensor(*[getattr(ops, ch) for ch in names])
+        M = S.tensor(*[S.PAULI[ch] for ch in names])
+        v = observable(reg[1:3], P)
+        assert abs(v.mean - np.trace(want @ M).real) < 4 / np.sqrt(N), (names, v.mean, np.trace(want @ M).real)
+    tot = 0.0                                               # purity 1 on every trajectory: sum over the Pauli basis of <P>^2 = 2^n
+    for a in "IXYZ":
+        for b in "IXYZ":
+            for d in "IXYZ":
+                v = observable(reg[1:3], ops.tensor(getattr(ops, a), getattr(ops, b), getattr(ops, d)))
+                tot += v.mean ** 2 + v.var
+    assert abs(tot - 8.0) < 1e-9
+    c.close()
