@@ -445,7 +445,7 @@ def cpu_bitsliced(g, ntraj, rank, world, no_cpu=False):
     res = {"value": n / dt, "unit": "trajectories/s", "cores": threads, "kind": "bit-sliced-c++-openmp",
            "sample": f"{n} trajectories of the same recorded program (lockstep masks) in {dt:.2f} s on {threads} OpenMP threads",
            "rows_equal_gpu": equal if n == ntraj else None,
-           "note": "the GPU design on the CPU: exported op records, csrc/qsb_tab_core.cuh compiled by g++ -O3 -march=native, one 32-trajectory word column per task"}
+           "note": "the GPU design on the CPU: exported op records, csrc/qsb_tab_core.cuh compiled by g++ -O3, one 32-trajectory word column per task"}
     if n == ntraj and not equal:
         raise RuntimeError(f"bit-sliced CPU replay disagrees with the GPU program: {res}")
     return res
