@@ -17,6 +17,7 @@ struct DTile {
     int lane, grp;
     uint32_t gmask;      // the lanes of this thread's group inside its warp (all 32 when T == 32)
     int gshift;          // position of the group's lane 0 inside the warp
+    uint32_t validw;     // lanes of the tile that are trajectories of the job
     __device__ __forceinline__ double2& at(int base, int e) const { return arena[(size_t)(base + e) * T + lane]; }
 };
 
@@ -303,9 +304,9 @@ __device__ __forceinline__ void d_expect(const DTile& t, const DExecOp& op, cons
         case 3: { const double x = re; re = im; im = -x; break; }
         default: break;
     }
-    const bool al = (t.masks[op.al[0]] >> t.lane) & 1u;
+    const bool al = ((t.masks[op.al[0]] & (a.live_word >= 0 ? t.masks[a.live_word] : 0xffffffffu)) >> t.lane) & 1u;   // retired lanes are tallied where they continue
     if (!al) { re = 0; im = 0; }
-    if (op.per_traj) { op.per_traj[2 * t_loc] = re; op.per_traj[2 * t_loc + 1] = im; }
+    if (op.per_traj && ((t.validw >> t.lane) & 1u) && (a.live_word < 0 || ((t.masks[a.live_word] >> t.lane) & 1u))) { op.per_traj[2 * t_loc] = re; op.per_traj[2 * t_loc + 1] = im; }
     if (op.stats) {
         double v[4] = {al ? 1.0 : 0.0, re, re * re, im};
 #pragma unroll
@@ -341,9 +342,16 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dense_exec(DExecArgs a0) {
     }
     const uint32_t tmask = t.T == 32 ? 0xffffffffu : ((1u << t.T) - 1u);
     for (int64_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
-        const int64_t t0 = tile << a.logT, t_loc = t0 + t.lane;
+        const int64_t t0 = tile << a.logT, pos = t0 + t.lane;                 // position inside the job
+        // lane subset (cohort re-runs): position p is the trajectory whose slot in the context is lanes[p]; draws, per-trajectory rows
+        // and retire codes are indexed by that slot, so every program of a tree writes into the same buffers
+        const int64_t t_loc = a.lanes ? (pos < a.count ? (int64_t)__ldg(a.lanes + pos) : 0) : pos;
         const uint64_t traj = a.traj0 + (uint64_t)t_loc;
-        const uint32_t validw = (a.valid[t0 >> 5] >> (t0 & 31)) & tmask;
+        uint32_t validw;
+        if (a.lanes) { const int64_t left = a.count - t0; validw = left >= t.T ? tmask : left > 0 ? ((1u << left) - 1u) : 0u; }
+        else validw = (a.valid[t0 >> 5] >> (t0 & 31)) & tmask;
+        t.validw = validw;
+        if (a.live_word >= 0 && threadIdx.x == 0) t.masks[a.live_word] = validw;   // published by the barrier of the first op-chunk refill
         for (int i = 0; i < a.nops; ++i) {
             if ((i % CHUNK) == 0) {   // refill (also the barrier between tiles)
                 __syncthreads();
@@ -408,6 +416,15 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dense_exec(DExecArgs a0) {
                 }
                 break;
             case TOP_KILL: if (threadIdx.x == 0) t.masks[op.al[0]] &= ~t.masks[op.m[0]]; break;
+            case TOP_RETIRE:   // cohort forking: these lanes leave the program (no later statistic counts them) and are tagged for the tree driver
+                if (t.grp == op.grp) {
+                    const uint32_t r = t.masks[op.m[0]] & t.masks[a.live_word];
+                    int32_t* const codes = reinterpret_cast<int32_t*>(op.per_traj);
+                    if (codes && ((r >> t.lane) & 1u)) codes[t_loc] = (int32_t)op.u[0];
+                    __syncwarp(t.gmask);
+                    if (t.lane == 0) t.masks[a.live_word] &= ~r;
+                }
+                break;
             case TOP_ALIVE_COPY: if (threadIdx.x == 0) t.masks[op.m[0]] = t.masks[op.al[0]]; break;
             default: break;
             }
@@ -423,6 +440,7 @@ struct qsb_dprogram {
     DExecOp* d_ops; DExecOp* h_ops; int nops;
     double* d_aux; int naux;
     int elems, nmasks, logT, blocks_per_sm, smem_bytes, barriers, threads, variant, aux_smem, regs, levels;
+    int live_word;                   // mask word of the cohort's live lanes (-1: no TOP_RETIRE in the program)
     uint64_t per_traj_rows, nstats;
 };
 
@@ -434,7 +452,7 @@ bool overlap(const std::vector<Span>& a, const std::vector<Span>& b) {
     for (auto& x : a) for (auto& y : b) if (x.lo < y.hi && y.lo < x.hi) return true;
     return false;
 }
-Access access_of(const TabOp& o) {
+Access access_of(const TabOp& o, int live = -1) {
     Access A;
     auto E = [](int base, int n) { return Span{base, base + (1 << (2 * n))}; };
     auto M = [](int w) { return Span{MASK0 + w, MASK0 + w + 1}; };
@@ -445,7 +463,8 @@ Access access_of(const TabOp& o) {
     case DOP_APPLY: A.r = {E(o.s[0], o.n)}; if (o.m[0] >= 0) A.r.push_back(M(o.m[0])); A.w = {E(o.s[0], o.n)}; break;
     case DOP_CHANNEL: case DOP_PTRACE: A.r = {E(o.s[0], o.n)}; A.w = {E(o.s[0], o.n)}; break;
     case DOP_MEASURE: A.r = {E(o.s[0], o.n), M(o.al[0]), Span{SCR, SCR + 1}}; A.w = {E(o.s[0], o.n), M(o.m[0]), Span{SCR, SCR + 1}}; break;
-    case DOP_EXPECT: A.r = {E(o.s[0], o.n), M(o.al[0])}; break;
+    case DOP_EXPECT: A.r = {E(o.s[0], o.n), M(o.al[0])}; if (live >= 0) A.r.push_back(M(live)); break;
+    case TOP_RETIRE: A.r = {M(o.m[0]), M(live)}; A.w = {M(live)}; break;
     case TOP_MASK_FILL: case TOP_MASK_RANDOM: A.w = {M(o.m[0])}; break;
     case TOP_MASK_LOGIC: A.r = {M(o.m[1])}; if (o.m[2] >= 0) A.r.push_back(M(o.m[2])); A.w = {M(o.m[0])}; break;
     case TOP_KILL: A.r = {M(o.al[0]), M(o.m[0])}; A.w = {M(o.al[0])}; break;
@@ -460,6 +479,8 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     qsb_dprogram* P = new qsb_dprogram();
     memset(P, 0, sizeof(*P));
     P->ctx = ctx; P->elems = elems > 0 ? elems : 1; P->nmasks = nmasks > 0 ? nmasks : 1;
+    P->live_word = -1;
+    for (auto& o : R->ops) if (o.type == TOP_RETIRE) { P->live_word = P->nmasks; P->nmasks += 1; break; }   // one more mask word: the cohort's live lanes
     // ops, barrier flags, group assignment
     std::vector<DExecOp> xops;
     std::vector<double> aux = R->daux;
@@ -522,7 +543,7 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     std::vector<int> level(xops.size(), 0);
     if (!getenv("QSB_DEXEC_NOSCHED") && xops.size() > 1) {
         std::vector<Access> accs(xops.size());
-        for (size_t j = 0; j < xops.size(); ++j) accs[j] = access_of(R->ops[src[j]]);
+        for (size_t j = 0; j < xops.size(); ++j) accs[j] = access_of(R->ops[src[j]], P->live_word);
         int nlev = 0;
         for (size_t j = 0; j < xops.size(); ++j) {
             int lv = 0;
@@ -608,7 +629,7 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
             if (level[j] != cur) { cur = level[j]; if (P->levels) rr = 0; }
             int items = 0;
             switch (x.type) {
-                case DOP_MEASURE: case DOP_EXPECT: case TOP_MASK_RANDOM: x.grp = (uint16_t)(rr % G); items = 1; break;
+                case DOP_MEASURE: case DOP_EXPECT: case TOP_MASK_RANDOM: case TOP_RETIRE: x.grp = (uint16_t)(rr % G); items = 1; break;
                 case DOP_CONST: case DOP_COPY: items = 1 << (2 * x.n); break;
                 case DOP_TENSOR: items = 1 << (2 * (x.n + x.n2)); break;
                 case DOP_APPLY: items = 1 << (2 * x.n - 2 * x.k); break;
@@ -624,7 +645,7 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
         Access acc;
         for (size_t j = 0; j < xops.size(); ++j) {
             const TabOp& o = R->ops[src[j]];
-            Access A = access_of(o);
+            Access A = access_of(o, P->live_word);
             bool need = overlap(A.w, acc.r) || overlap(A.w, acc.w) || overlap(A.r, acc.w);
             if ((j % chunk) == 0) { acc = Access(); need = false; }
             if (need) { xops[j].flags |= 1; P->barriers++; acc = Access(); }
@@ -651,11 +672,13 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     return QSB_OK;
 }
 
-int qsb_dexec_run(qsb_dprogram* P, uint64_t traj_shift, uint64_t draw_base) {
+int qsb_dexec_run(qsb_dprogram* P, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base) {
     qsb_ctx* ctx = P->ctx;
     DExecArgs a;
     a.ops = P->d_ops; a.nops = P->nops; a.aux = P->d_aux; a.elems = P->elems; a.nmasks = P->nmasks; a.logT = P->logT; a.aux_smem = P->aux_smem;
-    a.valid = ctx->valid; a.ntiles = ctx->npad >> P->logT;
+    a.valid = ctx->valid; a.ntiles = lanes_dev ? ((count + (1 << P->logT) - 1) >> P->logT) : (ctx->npad >> P->logT);
+    a.lanes = lanes_dev; a.count = lanes_dev ? count : ctx->ntraj; a.live_word = P->live_word;
+    if (a.ntiles == 0) return QSB_OK;
     a.seed = ctx->seed; a.traj0 = (uint64_t)ctx->traj_offset + traj_shift; a.draw_base = draw_base; a.flags = ctx->dev_flags;
     int64_t blocks = (int64_t)ctx->sm_count * P->blocks_per_sm;
     if (blocks > a.ntiles) blocks = a.ntiles;

@@ -45,6 +45,10 @@ struct DExecArgs {
     int64_t ntiles;
     uint64_t seed, traj0, draw_base;
     int* flags;                      // sticky device-side error flags of the context
+    // cohort forking (qsb_ctx_retire on a dense recording): the launch may cover a lane subset of the context
+    const uint32_t* lanes;           // lane index (trajectory slot of the context) of job position p; nullptr: identity
+    int64_t count;                   // trajectories of the job (lanes != nullptr)
+    int live_word;                   // mask word that holds the lanes still in this cohort (-1: the program never retires lanes)
 };
 
 // ---- the recorder (shared by qsb_exec.cu and qsb_dexec.cu) ------------------------------------------------
@@ -73,7 +77,7 @@ struct qsb_recorder {
 struct qsb_dprogram;                 // built by qsb_dexec_build from a dense recording
 // elems / nmasks: arena sizes after re-packing; the recorder's ops already carry the re-packed references
 int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dprogram** out);
-int qsb_dexec_run(qsb_dprogram* P, uint64_t traj_shift, uint64_t draw_base);
+int qsb_dexec_run(qsb_dprogram* P, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base);
 int qsb_dexec_upload(qsb_dprogram* P, int64_t* bytes);
 void qsb_dexec_info(const qsb_dprogram* P, int64_t info[8]);
 void qsb_dexec_free(qsb_dprogram* P);

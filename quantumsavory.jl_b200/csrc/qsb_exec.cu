@@ -694,8 +694,7 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
     for (int j = 0; j < n; ++j) {
         if (!in[j].P || in[j].P->ctx != ctx) QSB_FAIL(QSB_ERR_BAD_ARG, "job %d: null program or program of another context", j);
         if (in[j].count < 0 || in[j].count > ctx->ntraj) QSB_FAIL(QSB_ERR_BAD_ARG, "job %d: %lld lanes requested from an ensemble of %lld", j, (long long)in[j].count, (long long)ctx->ntraj);
-        if (in[j].P->dprog && (n > 1 || in[j].lanes || in[j].count != ctx->ntraj || (flags & QSB_RUN_KEEP_STATS)))
-            QSB_FAIL(QSB_ERR_UNSUPPORTED, "dense programs run on the whole ensemble, one program per launch");
+        if ((in[j].P->dprog != nullptr) != (in[0].P->dprog != nullptr)) QSB_FAIL(QSB_ERR_UNSUPPORTED, "a launch runs tableau programs or dense programs, not both");
     }
     if (!(flags & QSB_RUN_KEEP_STATS)) {
         for (int j = 0; j < n; ++j) {
@@ -706,10 +705,12 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
             QSB_LAUNCH_CHECK(ctx);
         }
     }
-    if (n == 1 && in[0].P->dprog) {
-        qsb_program* P = in[0].P;
-        QSB_TRY(qsb_dexec_run(P->dprog, traj_shift, draw_base));
-        ctx->ops += P->ops_per_run; ctx->draws += P->draws_per_run;
+    if (in[0].P->dprog) {   // dense programs: one launch per (program, lane subset) job -- a tile of trajectories is a block's whole working set
+        for (int j = 0; j < n; ++j) {
+            qsb_program* P = in[j].P;
+            QSB_TRY(qsb_dexec_run(P->dprog, in[j].lanes, in[j].count, traj_shift, draw_base));
+            ctx->ops += P->ops_per_run / (uint64_t)ctx->ntraj * (uint64_t)in[j].count; ctx->draws += P->draws_per_run;
+        }
         return QSB_OK;
     }
     std::vector<ExecJob> jobs(n);
@@ -811,8 +812,6 @@ extern "C" int qsb_ctx_retire(qsb_ctx* ctx, const qsb_mask* lanes, int32_t code,
     if (!ctx || !lanes) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_ctx_retire: null argument");
     if (!ctx->rec) QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_ctx_retire needs a recording: cohorts are re-run as recorded programs over lane subsets");
     QSB_TRY(qsb_handle_ok(ctx, lanes->vplane >= 0, lanes->gen));
-    if (ctx->rec->dense) QSB_FAIL(QSB_ERR_UNSUPPORTED, "cohort forking of dense programs is not implemented");
-    QSB_TRY(qsb_rec_set_family(ctx, false));
     TabOp* o = qsb_rec_push(ctx, TOP_RETIRE);
     o->m[0] = lanes->vplane; o->u[0] = (uint32_t)code; o->per_traj = reinterpret_cast<double*>(codes_dev);
     return QSB_OK;

@@ -148,3 +148,56 @@ def test_wave_of_lane_subsets_equals_separate_runs():
     assert torch.equal(rows[0][0], stats.t) and torch.equal(rows[0][1], per) and torch.equal(rows[0][2], tree.codes)
     assert (tree.codes >= 0).any()
     tree.free(); ctx.close()
+
+
+def test_dense_programs_fork_too():
+    """The same lane-by-lane check in the density-matrix formalism (BASELINE configs[0]): cohort forking of DENSE recorded
+    programs -- k_dense_exec with lane subsets, a live-lanes word and TOP_RETIRE.  Every lane against its oracle twin at every
+    sampling point (1e-12), statistics rows against the sums over the twins."""
+    import torch
+    from qsb200 import symbols as S
+    from qsb200.backend import BatchContext, CudaBatchRepr
+    from qsb200.cohorts import CohortTree
+    from qsb200.registers import dispose, observable_options
+    from qsb200.sharding import StatsBuffer
+    from qsb200.workloads import firstgenrepeater as fgr
+    from tests.oracle_backend import OracleContext, OracleRepr
+    ntraj, bg = 150, S.T1T2Noise(60.0, 40.0)
+    kw = dict(sizes=(2, 3, 3, 2), F=0.95, t_end=8.0, dt_sample=0.2)
+    nrows = 2 * 41
+    ctx = BatchContext(ntraj, seed=SEED)
+    npad = (ntraj + 31) // 32 * 32
+    stats = StatsBuffer(nrows, "cuda:0")
+    per = torch.zeros(nrows, 2 * npad, dtype=torch.float64, device="cuda:0")
+    slot = [0]
+
+    def next_row():
+        i = slot[0]; slot[0] += 1
+        return stats.slot_ptr(i)
+
+    def schedule():
+        slot[0] = 0
+        with observable_options(stats_dev=next_row, sync=False, per_traj_dev=lambda: per[slot[0] - 1].data_ptr()):
+            _, _, net = fgr.monte_carlo_trajectory(lambda: CudaBatchRepr(ctx, "qo"), background=bg, **kw)
+        dispose(net.registers)
+        assert slot[0] == nrows
+
+    tree = CohortTree(ctx, schedule)
+    stats.t.zero_(); per.zero_(); torch.cuda.synchronize()
+    info = tree.run()
+    ctx.sync(); torch.cuda.synchronize()
+    got = per.view(nrows, -1, 2)[:, :ntraj, 0].cpu().numpy()
+    want, fails = [], []
+    for t in range(ntraj):
+        octx = OracleContext(SEED, t)
+        vals = []
+        _, _, net = fgr.monte_carlo_trajectory(lambda: OracleRepr(octx, "qo"), background=bg,
+                                               record=lambda k, tm, v: vals.append(float(np.real(complex(v)))), **kw)
+        want.append(vals); fails.append(net.log.get("failures", 0))
+    want, fails = np.array(want).T, np.array(fails)
+    assert (fails > 0).mean() > 0.2 and info["censored"] == 0 and info["dropped"] == 0
+    assert info["levels"] == fails.max() + 1 and info["lanes_rerun"] == fails.sum()
+    assert np.abs(got - want).max() < 1e-12, np.abs(got - want).max()
+    rows = stats.t.cpu().numpy()
+    assert np.abs(rows[:, 1] - want.sum(1)).max() < 1e-10 and np.abs(rows[:, 2] - (want * want).sum(1)).max() < 1e-10
+    tree.free(); ctx.close()
