@@ -118,6 +118,9 @@ WORKLOADS = {
                                                  "(failed purifications = per-trajectory masks; NOT the reference's per-trajectory control flow: round-1 headline, kept for continuity)"),
     "firstgenrepeater_dm": dict(fn=wl_fgr, formalism="qo", ntraj=1_000_000, mode="program",
                                 desc=FGR_DESC + ", QuantumOpticsRepr dm, T1T2Noise(1000,100), t=0:0.2:25; lockstep masks ensemble"),
+    "firstgenrepeater_dm_cohort": dict(fn=wl_fgr, formalism="qo", ntraj=1_000_000, mode="cohort",
+                                       desc=FGR_DESC + ", QuantumOpticsRepr dm, T1T2Noise(1000,100), t=0:0.2:25; cohort tree of DENSE recorded programs: "
+                                            "every trajectory follows its own control flow (the reference's semantics)"),
     "firstgenrepeater_dm_ref5": dict(fn=wl_fgr_ref5, formalism="qo", ntraj=1_000_000, mode="program",
                                      desc="examples/firstgenrepeater/3_purifier_example.jl parameters: sizes [2,3,4,3,2], F=0.9, T2Dephasing(10), t=0:0.2:30, dm; lockstep masks ensemble"),
     "firstgenrepeater_dm_t1t2_4": dict(fn=wl_fgr_t1t2_4, formalism="qo", ntraj=1_000_000, mode="program",
@@ -132,7 +135,7 @@ WORKLOADS = {
     "sweep12_dm": dict(fn=wl_sweep12, formalism="qo", ntraj=256, mode="per_op",
                        desc="12-qubit composed dm register: random H/X/Z + CNOT, T1T2Noise(100,10) on every qubit, project_traceout!, recompose"),
 }
-DEFAULT_EXTRAS = "firstgenrepeater_clifford_masks,firstgenrepeater_dm,firstgenrepeater_dm_ref5,firstgenrepeater_dm_t1t2_4,firstgenrepeater_mcket,ghz_sensors_dm,repeatergrid_clifford,sweep12_dm"
+DEFAULT_EXTRAS = "firstgenrepeater_clifford_masks,firstgenrepeater_dm,firstgenrepeater_dm_cohort,firstgenrepeater_dm_ref5,firstgenrepeater_dm_t1t2_4,firstgenrepeater_mcket,ghz_sensors_dm,repeatergrid_clifford,sweep12_dm"
 
 
 # ------------------------------------------------------------------------------------------------
@@ -142,7 +145,7 @@ DEFAULT_EXTRAS = "firstgenrepeater_clifford_masks,firstgenrepeater_dm,firstgenre
 # interpreter bound, kept beside it as cpu_baseline_python).
 # ------------------------------------------------------------------------------------------------
 CPU_SAMPLE = {   # trajectories per timed CPU pass (about 5-20 s of work on 16 cores), Python-driven trajectories per core
-    "firstgenrepeater_clifford": (100_000, 40), "firstgenrepeater_clifford_masks": (0, 0), "firstgenrepeater_dm": (4_000, 0),
+    "firstgenrepeater_clifford": (100_000, 40), "firstgenrepeater_clifford_masks": (0, 0), "firstgenrepeater_dm": (4_000, 0), "firstgenrepeater_dm_cohort": (4_000, 0),
     "firstgenrepeater_dm_ref5": (4_000, 0), "firstgenrepeater_dm_t1t2_4": (4_000, 0), "firstgenrepeater_mcket": (40_000, 0),
     "ghz_sensors_dm": (16, 0), "repeatergrid_clifford": (20_000, 0), "sweep12_dm": (0, 0)}
 
@@ -462,9 +465,13 @@ def parity_check_tree(g, cpu, n):
     g.stream.synchronize(); torch.cuda.synchronize()
     rows_gpu = g.stats.t[: g.nobs].cpu().numpy()[:, :3]
     rows_cpu = cpu["rows"][: g.nobs]
-    equal = bool(np.array_equal(rows_gpu, rows_cpu))
+    exact = g.w["formalism"] == "clifford"
+    # tableau rows are integer tallies (identical); dense rows are floating-point sums over the same per-trajectory values in a
+    # different order: identical alive counts, sums within 1e-12 x trajectories
+    equal = bool(np.array_equal(rows_gpu, rows_cpu)) if exact else bool(np.array_equal(rows_gpu[:, 0], rows_cpu[:, 0]) and np.abs(rows_gpu - rows_cpu).max() <= 1e-12 * n)
     res = {"rows": int(g.nobs), "equal": equal, "trajectories": n, "against": "oracle/qsb_replay.c (compiled CPU replay, every trajectory on its own control flow) on the same global trajectory ids and fork budget",
-           "tolerance": "bit-exact (integer tallies)", "max_abs_diff": float(np.abs(rows_gpu - rows_cpu).max()), "censored_gpu": info["censored"], "censored_cpu": cpu["censored"]}
+           "tolerance": "bit-exact (integer tallies)" if exact else "identical alive counts, sums within 1e-12 x trajectories",
+           "max_abs_diff": float(np.abs(rows_gpu - rows_cpu).max()), "censored_gpu": info["censored"], "censored_cpu": cpu["censored"]}
     if not equal or info["censored"] != cpu["censored"]:
         raise RuntimeError(f"cohort-tree parity check failed: {res}")
     return res
@@ -634,7 +641,7 @@ def fused_roofline(out, rows, g, workload, lanes, peak, which, clocks):
     have = True
     per_kernel = {}
     for r in fused:
-        f = ncu_facts(workload.replace("_masks", ""), r["kernel"])
+        f = ncu_facts(workload.replace("_masks", "").replace("_cohort", ""), r["kernel"])
         if not f:
             have = False
             continue

@@ -203,7 +203,8 @@ int qsb_program_run(qsb_program* prog, uint64_t traj_shift, uint64_t draw_base);
  * same draws: its run is identical up to the fork and continues on its own branch).  Statistics rows and per-trajectory
  * rows are indexed by lane index, so every program of the tree writes into the same buffers; flags & QSB_RUN_KEEP_STATS
  * accumulates into the statistics rows instead of zeroing them first.  qsb_wave_run executes any number of (program,
- * lane subset) jobs in ONE launch pair (tableau programs; lanes_dev[j] == NULL runs job j on the whole ensemble). */
+ * lane subset) jobs in ONE launch pair (tableau programs) or as one launch per job over a pool of streams (dense programs);
+ * lanes_dev[j] == NULL runs job j on the whole ensemble. */
 enum { QSB_RUN_KEEP_STATS = 1 };
 int qsb_ctx_retire(qsb_ctx* ctx, const qsb_mask* lanes, int32_t code, int32_t* codes_dev);
 int qsb_program_run_lanes(qsb_program* prog, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base, int flags);

@@ -672,8 +672,9 @@ int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dp
     return QSB_OK;
 }
 
-int qsb_dexec_run(qsb_dprogram* P, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base) {
+int qsb_dexec_run(qsb_dprogram* P, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base, cudaStream_t stream) {
     qsb_ctx* ctx = P->ctx;
+    if (!stream) stream = ctx->stream;
     DExecArgs a;
     a.ops = P->d_ops; a.nops = P->nops; a.aux = P->d_aux; a.elems = P->elems; a.nmasks = P->nmasks; a.logT = P->logT; a.aux_smem = P->aux_smem;
     a.valid = ctx->valid; a.ntiles = lanes_dev ? ((count + (1 << P->logT) - 1) >> P->logT) : (ctx->npad >> P->logT);
@@ -683,13 +684,13 @@ int qsb_dexec_run(qsb_dprogram* P, const uint32_t* lanes_dev, int64_t count, uin
     int64_t blocks = (int64_t)ctx->sm_count * P->blocks_per_sm;
     if (blocks > a.ntiles) blocks = a.ntiles;
     QSB_PRE(ctx, "k_dense_exec");
-    if (P->variant == 0) k_dense_exec<256, 1><<<(unsigned)blocks, 256, P->smem_bytes, ctx->stream>>>(a);
-    else if (P->variant == 1) k_dense_exec<256, 2><<<(unsigned)blocks, 256, P->smem_bytes, ctx->stream>>>(a);
-    else if (P->variant == 2) k_dense_exec<128, 4><<<(unsigned)blocks, 128, P->smem_bytes, ctx->stream>>>(a);
-    else if (P->variant == 3) k_dense_exec<32, 8><<<(unsigned)blocks, 32, P->smem_bytes, ctx->stream>>>(a);
-    else if (P->variant == 5) k_dense_exec<512, 1><<<(unsigned)blocks, 512, P->smem_bytes, ctx->stream>>>(a);
-    else if (P->variant == 6) k_dense_exec<1024, 1><<<(unsigned)blocks, 1024, P->smem_bytes, ctx->stream>>>(a);
-    else k_dense_exec<32, 16><<<(unsigned)blocks, 32, P->smem_bytes, ctx->stream>>>(a);
+    if (P->variant == 0) k_dense_exec<256, 1><<<(unsigned)blocks, 256, P->smem_bytes, stream>>>(a);
+    else if (P->variant == 1) k_dense_exec<256, 2><<<(unsigned)blocks, 256, P->smem_bytes, stream>>>(a);
+    else if (P->variant == 2) k_dense_exec<128, 4><<<(unsigned)blocks, 128, P->smem_bytes, stream>>>(a);
+    else if (P->variant == 3) k_dense_exec<32, 8><<<(unsigned)blocks, 32, P->smem_bytes, stream>>>(a);
+    else if (P->variant == 5) k_dense_exec<512, 1><<<(unsigned)blocks, 512, P->smem_bytes, stream>>>(a);
+    else if (P->variant == 6) k_dense_exec<1024, 1><<<(unsigned)blocks, 1024, P->smem_bytes, stream>>>(a);
+    else k_dense_exec<32, 16><<<(unsigned)blocks, 32, P->smem_bytes, stream>>>(a);
     QSB_LAUNCH_CHECK(ctx);
     // compulsory HBM traffic of the fused launch: op list + constants once, statistics and per-trajectory rows written once
     qsb_account(ctx, "k_dense_exec", (uint64_t)P->nops * sizeof(DExecOp) + (uint64_t)P->naux * 8 + P->nstats * 32 + P->per_traj_rows * (uint64_t)ctx->npad * 16);

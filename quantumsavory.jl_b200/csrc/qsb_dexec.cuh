@@ -77,7 +77,7 @@ struct qsb_recorder {
 struct qsb_dprogram;                 // built by qsb_dexec_build from a dense recording
 // elems / nmasks: arena sizes after re-packing; the recorder's ops already carry the re-packed references
 int qsb_dexec_build(qsb_ctx* ctx, qsb_recorder* R, int elems, int nmasks, qsb_dprogram** out);
-int qsb_dexec_run(qsb_dprogram* P, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base);
+int qsb_dexec_run(qsb_dprogram* P, const uint32_t* lanes_dev, int64_t count, uint64_t traj_shift, uint64_t draw_base, cudaStream_t stream = nullptr);   // stream: nullptr = the context's
 int qsb_dexec_upload(qsb_dprogram* P, int64_t* bytes);
 void qsb_dexec_info(const qsb_dprogram* P, int64_t info[8]);
 void qsb_dexec_free(qsb_dprogram* P);

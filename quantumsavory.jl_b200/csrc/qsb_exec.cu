@@ -706,10 +706,27 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
         }
     }
     if (in[0].P->dprog) {   // dense programs: one launch per (program, lane subset) job -- a tile of trajectories is a block's whole working set
+        // The cohorts of a tree level are independent and mostly small (a few tiles each, far fewer blocks than SMs), so their
+        // launches are dealt round-robin to a pool of side streams that fork from and join back into the context's stream.
+        const int NS = 8;
+        static thread_local cudaStream_t pool[64][NS];
+        static thread_local bool pool_ok[64];
+        const bool fan = n > 1 && !ctx->prof && ctx->device >= 0 && ctx->device < 64;
+        cudaEvent_t ev = nullptr;
+        if (fan) {
+            if (!pool_ok[ctx->device]) { for (int k = 0; k < NS; ++k) QSB_CUDA(cudaStreamCreateWithFlags(&pool[ctx->device][k], cudaStreamNonBlocking)); pool_ok[ctx->device] = true; }
+            QSB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            QSB_CUDA(cudaEventRecord(ev, ctx->stream));
+            for (int k = 0; k < NS && k < n; ++k) QSB_CUDA(cudaStreamWaitEvent(pool[ctx->device][k], ev, 0));
+        }
         for (int j = 0; j < n; ++j) {
             qsb_program* P = in[j].P;
-            QSB_TRY(qsb_dexec_run(P->dprog, in[j].lanes, in[j].count, traj_shift, draw_base));
+            QSB_TRY(qsb_dexec_run(P->dprog, in[j].lanes, in[j].count, traj_shift, draw_base, fan ? pool[ctx->device][j % NS] : nullptr));
             ctx->ops += P->ops_per_run / (uint64_t)ctx->ntraj * (uint64_t)in[j].count; ctx->draws += P->draws_per_run;
+        }
+        if (fan) {
+            for (int k = 0; k < NS && k < n; ++k) { QSB_CUDA(cudaEventRecord(ev, pool[ctx->device][k])); QSB_CUDA(cudaStreamWaitEvent(ctx->stream, ev, 0)); }
+            QSB_CUDA(cudaEventDestroy(ev));
         }
         return QSB_OK;
     }
