@@ -165,6 +165,31 @@ int qsb_ptrace(qsb_state* st, int idx, uint64_t draw_id);
 int qsb_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* obs, int obs_sign,
                double* per_traj_dev, double* stats_dev, double* stats_host);
 
+/* The Pauli-string case of qsb_expect (obs_kind == QSB_OBS_PAULI, dense kinds) for callers that must not allocate.
+ * No counterpart in the reference: QuantumSavory has no notion of who owns GPU memory.  qsb_expect keeps its reduction
+ * partials in a per-context buffer that it frees and re-allocates when a larger observable arrives; that is a problem
+ * for (i) a host whose HBM is already owned by another allocator (CUDA.jl's pool, torch's caching allocator), where an
+ * allocation made behind its back can fail or force a pool trim that stalls the whole device, and (ii) a loop with a
+ * latency bound per call, where the growth lands in the middle of the loop.  This variant calls no cudaMalloc / cudaFree
+ * / stream-ordered allocator and uploads nothing: the partials live in a device array built into the library, of
+ * QSB_STATIC_SCRATCH_BYTES, which every GPU that loads the library holds until the process exits.
+ *   - limit: 2 * nsplit * Npad + 4 * ceil(Npad / 256) doubles must fit (Npad = trajectories of the context rounded up to 32);
+ *     the call lowers its split count to fit and returns QSB_ERR_BAD_ARG with a message when the context has more than
+ *     QSB_STATIC_MAX_TRAJ trajectories.  Fewer splits = a different summation order than qsb_expect: values agree to
+ *     rounding (1e-12 in the tests), not bit for bit.
+ *   - codes: uint8_t[k], 0 I, 1 X, 2 Y, 3 Z on subsystem idx[j]; per_traj_dev / stats_dev as in qsb_expect (device pointers
+ *     owned by the caller, at least one non-NULL); there is no host-visible output and the call never synchronises.
+ *   - the first call on each device looks up the array's device address (it may make the CUDA runtime load the library's
+ *     code onto that device): make it once per device during set-up, before any stream capture is opened.
+ *   - ONE array per device is shared by all contexts and calls and keeps the previous call's partials.  Nothing needs
+ *     clearing (every slot read is written first by the same call), but two calls that can overlap on the GPU -- different
+ *     streams, no event between them -- race on it.  Calls on one stream are safe.
+ *   - refused: tableau states (their expectation uses no scratch), calls inside qsb_record_begin/_end. */
+#define QSB_STATIC_SCRATCH_BYTES 4194304 /* 4 MiB */
+#define QSB_STATIC_MAX_TRAJ 260096
+int qsb_expect_pauli_static(qsb_state* st, const int* idx, int k, const uint8_t* codes, int obs_sign,
+                            double* per_traj_dev, double* stats_dev);
+
 /* ---- per-trajectory masks --------------------------------------------------------------------*/
 int qsb_mask_create(qsb_ctx* ctx, int fill, qsb_mask** out);
 int qsb_mask_free(qsb_mask* m);

@@ -94,6 +94,7 @@ def _declare(L):
         "qsb_measure": (C.c_int, [vp, C.c_int, C.c_int, dp, C.c_uint64, vpp, vpp, i64p]),
         "qsb_ptrace": (C.c_int, [vp, C.c_int, C.c_uint64]),
         "qsb_expect": (C.c_int, [vp, ip, C.c_int, C.c_int, vp, C.c_int, vp, vp, dp]),
+        "qsb_expect_pauli_static": (C.c_int, [vp, ip, C.c_int, u8p, C.c_int, vp, vp]),
         "qsb_mask_create": (C.c_int, [vp, C.c_int, vpp]),
         "qsb_mask_free": (C.c_int, [vp]),
         "qsb_mask_logic": (C.c_int, [vp, vp, vp, C.c_int]),

@@ -1186,3 +1186,109 @@ int qsbd_expect(qsb_state* st, const int* idx, int k, int obs_kind, const void* 
     }
     return QSB_OK;
 }
+
+// =============================================================================================
+// qsb_expect_pauli_static: the Pauli-string observable for callers that must not allocate
+// =============================================================================================
+// qsb_expect keeps its reduction partials in ctx->scratch, which qsb_ensure_scratch frees and re-allocates from the
+// stream's memory pool whenever a larger observable arrives.  Two kinds of caller cannot live with that:
+//   - a host process whose GPU memory already belongs to somebody else's allocator (CUDA.jl's pool or torch's caching
+//     allocator holding nearly all of the HBM for a big density matrix): an allocation made behind its back can fail, or
+//     make the driver trim the other pool, which stalls every stream of the device;
+//   - a control loop with a latency bound per call (an observable evaluated between two events of a discrete-event
+//     run): growing the scratch buffer is a free + an allocation in the middle of the loop.
+// This variant does the same two passes (k_expect writes one partial sum per (split, trajectory), k_expect_finalize
+// folds them) with the partials in a file-scope device array of fixed size.  Cost: every GPU on which this library's
+// code gets loaded holds QSB_STATIC_SCRATCH_BYTES (4 MiB) for the life of the process, used or not.
+//
+// Sharing rules.  There is ONE array per device, shared by every context and every call.  The call leaves its partials
+// behind; nothing in it has to start at zero, because k_expect stores (never accumulates into) every slot that
+// k_expect_finalize reads, and k_expect_finalize stores every block-statistics slot that k_stats_final reads -- so no
+// clearing pass is needed and stale contents of an earlier, larger call are never read.  Two calls whose kernels can
+// overlap on the GPU (two contexts on different streams, or one context whose stream was swapped between the calls)
+// write the same slots and RACE: issue them on one stream or order them with an event.
+#define QSB_STATIC_SCRATCH_DOUBLES (QSB_STATIC_SCRATCH_BYTES / sizeof(double))
+static __device__ __align__(256) double g_static_scratch[QSB_STATIC_SCRATCH_DOUBLES];
+
+// In host code `g_static_scratch` is only a handle for the runtime's symbol table, not an address a kernel can use: the
+// device address differs per GPU and has to be asked for with that GPU current.  Looked up on the first call per device
+// and kept; that first call may make the runtime load this module onto the device, so it should not be made while a
+// stream capture is open.
+#define QSB_STATIC_MAX_DEVICES 64
+static double* g_static_scratch_dev[QSB_STATIC_MAX_DEVICES];
+static int static_scratch_address(const qsb_ctx* ctx, double** out) {
+    if (ctx->device < 0 || ctx->device >= QSB_STATIC_MAX_DEVICES)
+        QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_expect_pauli_static: device ordinal %d is beyond the %d devices the address table covers", ctx->device, QSB_STATIC_MAX_DEVICES);
+    double* p = __atomic_load_n(&g_static_scratch_dev[ctx->device], __ATOMIC_ACQUIRE);
+    if (!p) {
+        qsb_use_device(ctx);
+        void* sym = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&sym, g_static_scratch);
+        if (e != cudaSuccess || !sym) {
+            qsb_set_error("qsb_expect_pauli_static: cudaGetSymbolAddress of the built-in scratch array failed on device %d: %s", ctx->device, cudaGetErrorString(e));
+            cudaGetLastError();
+            return QSB_ERR_CUDA;
+        }
+        p = (double*)sym;   // every thread that gets here computes the same address, so a plain publish is enough
+        __atomic_store_n(&g_static_scratch_dev[ctx->device], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return QSB_OK;
+}
+
+extern "C" int qsb_expect_pauli_static(qsb_state* st, const int* idx, int k, const uint8_t* codes, int obs_sign,
+                                       double* per_traj_dev, double* stats_dev) {
+    if (!st || !idx || !codes) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_expect_pauli_static: null argument");
+    qsb_ctx* ctx = st->ctx;
+    if (ctx->rec) QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_expect_pauli_static cannot be recorded into a program (recorded observables keep their partials on chip; use qsb_expect)");
+    QSB_TRY(qsb_handle_ok(ctx, st->vbase >= 0, st->gen));
+    if (!qsb_is_dense(st->kind)) QSB_FAIL(QSB_ERR_UNSUPPORTED, "qsb_expect_pauli_static is defined for ket / density-matrix states (a tableau expectation needs no scratch: use qsb_expect)");
+    if (!per_traj_dev && !stats_dev) QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_expect_pauli_static: pass per_traj_dev, stats_dev or both (there is no host-visible output)");
+    const int n = st->n;
+    if (k < 1 || k > n) QSB_FAIL(QSB_ERR_BAD_INDEX, "%d indices given for a state of %d subsystems", k, n);
+    ExpArgs a; memset(&a, 0, sizeof(a));
+    a.n = n; a.k = k; a.is_ket = qsb_is_ketlike(st->kind); a.mode = 0;
+    int ny = 0;
+    for (int m = 0; m < k; ++m) {
+        if (idx[m] < 0 || idx[m] >= n) QSB_FAIL(QSB_ERR_BAD_INDEX, "subsystem index %d out of range for a state of %d subsystems", idx[m] + 1, n);
+        for (int b = 0; b < m; ++b) if (idx[m] == idx[b]) QSB_FAIL(QSB_ERR_BAD_INDEX, "subsystem index %d repeated", idx[m] + 1);
+        if (codes[m] > 3) QSB_FAIL(QSB_ERR_BAD_ARG, "bad Pauli code %d", codes[m]);
+        if (codes[m] == 1 || codes[m] == 2) a.xmask |= (size_t)1 << idx[m];
+        if (codes[m] == 3 || codes[m] == 2) a.zmask |= (size_t)1 << idx[m];
+        if (codes[m] == 2) ++ny;
+    }
+    // same global factor as qsbd_expect: P|c> = i^ny (-1)^{popc(c & zmask)} |c ^ xmask>
+    static const double2 ipow[4] = {{1, 0}, {0, 1}, {-1, 0}, {0, -1}};
+    const double sgn = obs_sign ? -1.0 : 1.0;
+    const double2 factor = make_double2(ipow[ny & 3].x * sgn, ipow[ny & 3].y * sgn);
+    const size_t range = (size_t)1 << n;
+
+    // layout inside the array: [partials 2 * nsplit * npad][block statistics 4 * fblocks].  The split count is the one
+    // qsb_expect would pick, lowered until the partials fit; when even one split does not fit the ensemble is too large.
+    const unsigned fblocks = (unsigned)((ctx->npad + 255) / 256);
+    const size_t fixed = (size_t)fblocks * 4, per_split = (size_t)2 * ctx->npad;
+    if (fixed + per_split > QSB_STATIC_SCRATCH_DOUBLES)
+        QSB_FAIL(QSB_ERR_BAD_ARG, "qsb_expect_pauli_static: %lld trajectories need %zu bytes of reduction scratch but the built-in array holds %zu "
+                 "(at most %zu trajectories per context); use qsb_expect, which allocates", (long long)ctx->ntraj,
+                 (fixed + per_split) * sizeof(double), (size_t)QSB_STATIC_SCRATCH_BYTES, (size_t)QSB_STATIC_MAX_TRAJ);
+    int nsplit = plan_split(ctx, range);
+    const size_t fit = (QSB_STATIC_SCRATCH_DOUBLES - fixed) / per_split;
+    if ((size_t)nsplit > fit) nsplit = (int)fit;
+
+    double* scratch = nullptr;
+    QSB_TRY(static_scratch_address(ctx, &scratch));
+    double* blockstats = scratch + (size_t)nsplit * per_split;
+    qsb_use_device(ctx);
+    dim3 grid((unsigned)((ctx->npad + TPB - 1) / TPB), nsplit, 1);
+    k_expect<<<grid, TPB, 0, ctx->stream>>>((const double2*)st->data, ctx->npad, a, range, nsplit, scratch);
+    k_expect_finalize<<<fblocks, 256, 0, ctx->stream>>>(scratch, nsplit, ctx->npad, factor, 0, st->alive, per_traj_dev, blockstats);
+    int launched = 2;
+    if (stats_dev) { k_stats_final<<<1, 256, 0, ctx->stream>>>(blockstats, (int)fblocks, stats_dev); ++launched; }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) QSB_FAIL(QSB_ERR_CUDA, "qsb_expect_pauli_static: kernel launch failed: %s", cudaGetErrorString(e));
+    // plain counters only: the per-kernel profile rows of qsb_ctx_profile grow host containers and create events
+    ctx->launches += launched;
+    ctx->algo_bytes += (uint64_t)16 * range * (a.is_ket ? 2 : 1) * ctx->ntraj;
+    ctx->ops += ctx->ntraj;
+    return QSB_OK;
+}
