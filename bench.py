@@ -23,6 +23,13 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# The CPU arms (cpu_baseline*, --impl reference) run on rank 0 with ALL the host cores this process may use, whatever the
+# launcher exported: torch.distributed.run sets OMP_NUM_THREADS=1, which made the round-2 reference arm a one-thread run at
+# N > 1.  Set before any OpenMP runtime is loaded, and passed to qsr_run explicitly as well.
+HOST_THREADS = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+if int(os.environ.get("RANK", 0)) == 0:
+    os.environ["OMP_NUM_THREADS"] = str(HOST_THREADS)
+
 import numpy as np  # noqa: E402
 
 SEED = 0x5153
@@ -172,13 +179,16 @@ def cpu_compiled(workload, ntraj, max_depth, traj_lo=0, passes=1, tree=None):
     (the GPU arm records its programs untimed too); the timed region is the compiled replay of `ntraj` trajectories."""
     from oracle import trace
     tree = tree or make_trace_tree(workload, max_depth)
-    r = tree.run(SEED, traj_lo, traj_lo + ntraj)          # grows the tree until every history of the sample is traced
+    r = tree.run(SEED, traj_lo, traj_lo + ntraj, threads=HOST_THREADS)   # grows the tree until every history of the sample is traced
     secs = [r["seconds"]] if r["passes"] == 1 else []
     while len(secs) < passes:
-        r = tree.run(SEED, traj_lo, traj_lo + ntraj)
+        r = tree.run(SEED, traj_lo, traj_lo + ntraj, threads=HOST_THREADS)
         secs.append(r["seconds"])
     s = float(np.median(secs))
-    return dict(value=(r["complete"]) / s, seconds=s, cores=trace.lib().qsr_max_threads(), nodes=r["nodes"], trace_s=tree.trace_s,
+    cores = int(trace.lib().qsr_max_threads())             # what omp_set_num_threads(HOST_THREADS) left in force
+    if cores == 1 and (os.cpu_count() or 1) > 1 and HOST_THREADS > 1:
+        raise RuntimeError("the compiled CPU replay ran on one thread of a multi-core box: refusing to report it as the CPU arm")
+    return dict(value=(r["complete"]) / s, seconds=s, cores=cores, nodes=r["nodes"], trace_s=tree.trace_s,
                 censored=r["censored"], complete=r["complete"], rows=r["rows"], tree=tree)
 
 
@@ -198,7 +208,7 @@ def _cpu_worker(args):
 def cpu_python(workload, per_core, cores=None):
     """Times `per_core` trajectories on each host core, oracle driven op by op from Python (processes, not threads)."""
     import multiprocessing as mp
-    cores = cores or os.cpu_count() or 1
+    cores = cores or HOST_THREADS
     jobs = [(workload, c * per_core, (c + 1) * per_core) for c in range(cores)]
     with mp.get_context("fork").Pool(cores) as pool:
         pool.map(_cpu_worker, [(workload, 0, 1)] * cores)     # pool start-up and imports are not timed
@@ -273,6 +283,24 @@ def ncu_facts(workload, kernel):
             return json.load(f).get(f"{workload}|{kernel}")
     except Exception:
         return None
+
+
+def ncu_facts_provenance(kernels):
+    """-> (commit the captures were taken at, [kernel source files that changed since]).  The facts are only as good as the
+    kernels they were captured from: profiles/ncu_kernels.json records a hash of every source file per kernel."""
+    import hashlib
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_kernels.json")) as f:
+            about = json.load(f).get("_about", {})
+        changed = set()
+        for k in kernels:
+            for src in about.get("kernel_sources", {}).get(k, []):
+                with open(os.path.join(ROOT, "quantumsavory.jl_b200", "csrc", src), "rb") as f:
+                    if hashlib.sha256(f.read()).hexdigest()[:16] != about.get("sources_sha256_16", {}).get(src):
+                        changed.add(src)
+        return about.get("captured_at_commit"), sorted(changed)
+    except Exception:
+        return None, ["(provenance unreadable)"]
 
 
 def measured_peak():
@@ -606,13 +634,13 @@ def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, pr
         top = rows[0]
         out["kernels"] = rows[:8]
         facts = ncu_facts(workload, top["kernel"])
-        out["roofline"] = {"bound": "hbm", "kernel": top["kernel"], "achieved": min(top["gbs"], peak), "peak": peak, "unit": "GB/s",
-                           "frac": min(top["gbs"] / peak, 1.0), "traffic": facts["dram_bytes"] if facts else None, "peak_source": which,
+        out["roofline"] = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["gbs"], "peak": peak, "unit": "GB/s",
+                           "frac": top["gbs"] / peak, "traffic": facts["dram_bytes"] if facts else None, "peak_source": which,
                            "algo_bytes_per_launch": top["algo_bytes"] / top["launches"], "us_per_launch": top["us_per_launch"],
                            "share_of_step": top["share"]}
         if top["gbs"] > peak:
             out["roofline"]["note"] = (f"algorithmic bytes / event time = {top['gbs']:.0f} GB/s exceeds the measured copy peak: launches of a few microseconds whose operands are "
-                                       "partly served by the 126 MB L2; achieved and frac are capped at the peak")
+                                       "partly served by the 126 MB L2 (or over-counted algorithmic bytes); reported as measured, not capped")
         if program or cohort:
             out["roofline"] = fused_roofline(out, rows, g, workload, ntraj * chunks, peak, which, clocks)
     if keep is not None:
@@ -650,7 +678,12 @@ def fused_roofline(out, rows, g, workload, lanes, peak, which, clocks):
         per_kernel[r["kernel"]] = {"ms": r["ms"], "issue_frac": f["warp_inst"] * scale / (sms * 4 * sm_hz * r["ms"] * 1e-3),
                                    "ncu": {k: f[k] for k in ("grid", "block", "issue_active", "source") if k in f}}
     issue_peak = sms * 4 * sm_hz                       # warp instructions per second the device can issue
-    blk = {"bound": "issue", "kernel": kname, "unit": "warp-inst/s", "peak": issue_peak, "peak_source": f"{sms} SMs x 4 schedulers x {sm_hz / 1e6:.0f} MHz (SM clock sampled under load)",
+    facts_commit, facts_changed = ncu_facts_provenance([r["kernel"] for r in fused])
+    blk = {"modelled": True,
+           "source": f"kernel time: CUDA events in this run; warp instructions and DRAM bytes: ncu captures of the single-program launch at commit {facts_commit} "
+                     "(profiles/ncu_kernels.json), scaled linearly by lanes processed -- the multi-job wave launches of a cohort tree were not captured themselves",
+           "facts_stale": facts_changed or None,       # kernel source files edited since the capture: the counts may no longer describe this build
+           "bound": "issue", "kernel": kname, "unit": "warp-inst/s", "peak": issue_peak, "peak_source": f"{sms} SMs x 4 schedulers x {sm_hz / 1e6:.0f} MHz (SM clock sampled under load)",
            "achieved": inst / sec if have else None, "frac": inst / sec / issue_peak if have else None,
            "traffic": dram if have else None, "traffic_source": "profiles/ncu_kernels.json (dram__bytes_read.sum + dram__bytes_write.sum of the ncu --set full captures, scaled to the lanes of this step)",
            "us_per_step": sec * 1e6, "share_of_step": sum(r["share"] for r in fused), "per_kernel": per_kernel,
@@ -669,6 +702,62 @@ def _emit(line: dict):
     os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
 
 
+HEADLINE_MAX_BYTES = 4000      # the driver keeps a tail of stdout: round 2's 34.6 KB line could not be parsed from it
+
+
+def _short(x, n=160):
+    return x if not isinstance(x, str) or len(x) <= n else x[: n - 3] + "..."
+
+
+def _headline(full: dict) -> dict:
+    """The compact record for stdout (<= HEADLINE_MAX_BYTES).  The full record (kernel tables, per-workload extras, logs) goes to
+    the side file named in `details`.  Long prose is cut, then optional keys are dropped, until the line fits."""
+    keys = ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype", "data",
+            "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline", "parity_check", "ensemble", "state_ops_per_sec",
+            "useful_state_ops_per_sec", "cpu_baseline_optimised", "alive_at_end_fraction", "extra", "details")
+    line = {k: full[k] for k in keys if k in full}
+    if isinstance(line.get("config"), dict):
+        line["config"] = {k: _short(v) for k, v in line["config"].items()}
+    if isinstance(line.get("clocks"), dict):
+        line["clocks"] = {k: line["clocks"][k] for k in ("sm_mhz", "sm_max_mhz", "reasons", "power_w_max", "samples") if k in line["clocks"]}
+    if isinstance(line.get("e2e"), dict):
+        line["e2e"] = {k: _short(v, 120) for k, v in line["e2e"].items()}
+    if isinstance(line.get("roofline"), dict):
+        r = line["roofline"]
+        line["roofline"] = {k: _short(r[k], 120) for k in ("bound", "kernel", "achieved", "peak", "unit", "frac", "traffic", "peak_source", "modelled", "facts_stale", "note", "source") if k in r}
+    for k in ("cpu_baseline", "cpu_baseline_optimised"):
+        if isinstance(line.get(k), dict):
+            line[k] = {kk: _short(v, 220) for kk, v in line[k].items() if kk != "note"}
+    if isinstance(line.get("parity_check"), dict):
+        line["parity_check"] = {k: _short(v, 100) for k, v in line["parity_check"].items()}
+    if isinstance(line.get("ensemble"), dict):
+        e = line["ensemble"]
+        line["ensemble"] = {k: e[k] for k in ("complete_fraction", "censored_fraction", "lane_runs_per_trajectory", "programs", "levels", "max_forks_per_trajectory",
+                                              "tree_record_ms") if k in e}
+    if isinstance(line.get("extra"), dict):      # one number per extra workload; everything else is in the side file
+        line["extra"] = {n: ({"value": v.get("value"), "ms_per_step": v.get("dev_ms_per_step"),
+                              "roofline_frac": (v.get("roofline") or {}).get("frac")} if "error" not in v else {"error": _short(v["error"], 80)})
+                         for n, v in line["extra"].items()}
+    for drop in (None, "extra", "cpu_baseline_optimised", "alive_at_end_fraction", "parity_check", "ensemble"):
+        if drop:
+            line.pop(drop, None)
+        if len(json.dumps(line)) <= HEADLINE_MAX_BYTES:
+            break
+    return line
+
+
+def _write_details(full: dict, path: str):
+    """Full record -> side file (and nothing on stdout).  Returns the path written, or None."""
+    try:
+        os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+        with open(path, "w") as f:
+            json.dump(full, f, indent=1)
+        return path
+    except OSError as e:
+        print(f"[bench] could not write {path}: {e}", file=sys.stderr)
+        return None
+
+
 _REAL_STDOUT = 1
 
 
@@ -685,6 +774,7 @@ def main():
     ap.add_argument("--workload", default="firstgenrepeater_clifford", choices=sorted(WORKLOADS))
     ap.add_argument("--ntraj", type=int, default=0, help="trajectories per GPU (default: the config's)")
     ap.add_argument("--extras", default=DEFAULT_EXTRAS, help="extra workloads reported under 'extra' (N=1 only, except sweep12_dm)")
+    ap.add_argument("--extras-out", default="", help="side file for the full record (kernel tables, per-workload extras); default gpurun_out/bench_extra_n<N>.json")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--mode", default="auto", choices=["auto", "per_op", "program", "cohort"],
                     help="cohort: tree of recorded programs, every trajectory on its own control flow; program: one recorded op list "
@@ -742,8 +832,9 @@ def main():
                                 keep=kept if (mode == "cohort" and rank == 0 and world == 1 and not args.no_cpu) else None)
     cpu = cpu_py = None
     parity = main_res.get("parity_check")
-    if rank == 0 and world == 1 and not args.no_cpu and CPU_SAMPLE.get(args.workload, (0, 0))[0]:
-        cpu, cpu_py, craw = cpu_baseline_for(args.workload, args.cohort_depth if mode == "cohort" else None)
+    if rank == 0 and not args.no_cpu and CPU_SAMPLE.get(args.workload, (0, 0))[0]:
+        # rank 0 at every N (same sample, all host cores), so that each line carries its own same-run CPU denominator
+        cpu, cpu_py, craw = cpu_baseline_for(args.workload, args.cohort_depth if mode == "cohort" else None, want_python=(world == 1))
         if kept:
             # cross-check of the two arms: the same trajectory ids through the GPU tree and the compiled CPU replay
             n = 4096
@@ -792,7 +883,13 @@ def main():
                 "roofline": main_res.get("roofline"), "kernels": main_res.get("kernels"), "cpu_baseline": cpu, "cpu_baseline_python": cpu_py,
                 "cpu_baseline_optimised": main_res.get("cpu_baseline_optimised"),
                 "workload_log": main_res["log"], "extra": extra}
-        _emit(line)
+        ens = main_res.get("ensemble") or {}
+        # ops of the lanes' FIRST run only: a cohort tree re-runs a forked lane from t = 0, state_ops_per_sec counts that work too
+        line["useful_state_ops_per_sec"] = line["state_ops_per_sec"] / ens["lane_runs_per_trajectory"] if ens.get("lane_runs_per_trajectory") else line["state_ops_per_sec"]
+        line["details"] = _write_details(line, args.extras_out or os.path.join(ROOT, "gpurun_out", f"bench_extra_n{world}.json"))
+        head = _headline(line)
+        assert len(json.dumps(head)) <= HEADLINE_MAX_BYTES, len(json.dumps(head))
+        _emit(head)
     if world > 1:
         dist.destroy_process_group()
 
