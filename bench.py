@@ -734,9 +734,8 @@ def _headline(full: dict) -> dict:
         e = line["ensemble"]
         line["ensemble"] = {k: e[k] for k in ("complete_fraction", "censored_fraction", "lane_runs_per_trajectory", "programs", "levels", "max_forks_per_trajectory",
                                               "tree_record_ms") if k in e}
-    if isinstance(line.get("extra"), dict):      # one number per extra workload; everything else is in the side file
-        line["extra"] = {n: ({"value": v.get("value"), "ms_per_step": v.get("dev_ms_per_step"),
-                              "roofline_frac": (v.get("roofline") or {}).get("frac")} if "error" not in v else {"error": _short(v["error"], 80)})
+    if isinstance(line.get("extra"), dict):      # one number per extra workload (same unit as `value`); everything else is in the side file
+        line["extra"] = {n: (float(f"{v['value']:.4g}") if isinstance(v.get("value"), (int, float)) else "error: " + _short(str(v.get("error")), 60))
                          for n, v in line["extra"].items()}
     for drop in (None, "extra", "cpu_baseline_optimised", "alive_at_end_fraction", "parity_check", "ensemble"):
         if drop:

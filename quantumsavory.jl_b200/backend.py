@@ -609,15 +609,18 @@ def _tab_dense_observable(self, indices, mat, stats_dev):
         _WARNED_DENSE_ON_TAB[0] = True
         warnings.warn("dense observable on a Clifford stabilizer state: evaluated as %d Pauli expectations (event :stabilizer_to_ket of the reference)" % 4 ** k)
     npad = (ctx.ntraj + 31) // 32 * 32
-    acc = torch.zeros(npad, dtype=torch.complex128, device=f"cuda:{ctx.device}")
     buf = torch.empty(2 * npad, dtype=torch.float64, device=f"cuda:{ctx.device}")
+    torch.cuda.current_stream(ctx.device).synchronize()   # the block may carry pending work of torch's stream; the library writes it on its own
+    acc = np.zeros(npad, np.complex128)
     stats = np.zeros(4)
     n_alive = 0.0
     for codes, c in _pauli_decomposition(mat, k):
         check(ctx.L.qsb_expect(self.p, _idx0(indices), k, _lib.OBS_PAULI, codes.ctypes.data_as(C.c_void_p), 0, C.c_void_p(buf.data_ptr()), None, _dp(stats)))
         n_alive = stats[0]
-        acc += c * buf[0::2]            # qsb_expect has synchronised (stats_host): the row is complete; dead lanes hold 0
-    vals = acc.cpu().numpy()[: ctx.ntraj]
+        # qsb_expect has synchronised (stats_host): the row is complete.  Accumulate on the host from a blocking copy, so that the next
+        # term's write of `buf` (context stream) cannot overtake a read still queued on torch's stream.  Dead lanes hold 0.
+        acc += c * buf.cpu().numpy()[0::2]
+    vals = acc[: ctx.ntraj]
     out = np.array([n_alive, vals.real.sum(), (vals.real ** 2).sum(), vals.imag.sum()])
     return BatchValue(ctx, out, vals)
 

@@ -175,6 +175,7 @@ class CohortTree:
             check(L.qsb_cohort_scatter(ctx.p, codes_p, node_p, nn, md, CENSORED, offsets.ctypes.data_as(C.c_void_p), child.ctypes.data_as(C.c_void_p), C.c_void_p(base)))
             h2d += offsets.nbytes + child.nbytes
             if not jobs:
+                ctx.sync()      # the scatter is still writing codes / lane_node on the context's stream; the next run() resets them on torch's
                 break
             self._launch(jobs, traj_shift)
             rerun += off

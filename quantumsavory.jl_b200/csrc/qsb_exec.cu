@@ -668,7 +668,14 @@ extern "C" int qsb_record_end(qsb_ctx* ctx, qsb_program** out) {
     }
     delete R;
     ctx->rec = nullptr;
-    if (rc != QSB_OK) { if (P->h_ops) cudaFreeHost(P->h_ops); delete P; return rc; }
+    if (rc != QSB_OK) {   // release whatever was uploaded before the failure (stream ordered; null pointers are skipped)
+        qsb_dev_free(ctx, P->d_ops); qsb_dev_free(ctx, P->d_obs); qsb_dev_free(ctx, P->d_stats);
+        qsb_dev_free(ctx, P->d_specs); qsb_dev_free(ctx, P->d_items); qsb_dev_free(ctx, P->d_aux);
+        if (P->arena) qsb_dev_free(ctx, P->arena);
+        if (P->h_ops) cudaFreeHost(P->h_ops);
+        delete P;
+        return rc;
+    }
     *out = P;
     return QSB_OK;
 }
@@ -729,6 +736,23 @@ static int run_wave(qsb_ctx* ctx, const WaveJobIn* in, int n, uint64_t traj_shif
             QSB_CUDA(cudaEventDestroy(ev));
         }
         return QSB_OK;
+    }
+    // A program whose arena lives in global memory (too many planes for a shared-memory tile, or too many waves) cannot share a
+    // launch: the global-arena instantiation is shaped for one job.  A level of a cohort tree may mix both kinds, so such jobs go
+    // out one launch pair each, on the same stream, and the shared-memory jobs keep their common launch.  Statistics rows were
+    // zeroed above where asked, hence KEEP_STATS below.
+    if (n > 1) {
+        int with_arena = 0;
+        for (int j = 0; j < n; ++j) with_arena += in[j].P->arena != nullptr;
+        if (with_arena) {
+            std::vector<WaveJobIn> tiled;
+            for (int j = 0; j < n; ++j) {
+                if (in[j].P->arena) QSB_TRY(run_wave(ctx, &in[j], 1, traj_shift, draw_base, flags | QSB_RUN_KEEP_STATS));
+                else tiled.push_back(in[j]);
+            }
+            if (!tiled.empty()) QSB_TRY(run_wave(ctx, tiled.data(), (int)tiled.size(), traj_shift, draw_base, flags | QSB_RUN_KEEP_STATS));
+            return QSB_OK;
+        }
     }
     std::vector<ExecJob> jobs(n);
     std::vector<uint32_t> words(n);

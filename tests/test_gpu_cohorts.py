@@ -201,3 +201,57 @@ def test_dense_programs_fork_too():
     rows = stats.t.cpu().numpy()
     assert np.abs(rows[:, 1] - want.sum(1)).max() < 1e-10 and np.abs(rows[:, 2] - (want * want).sum(1)).max() < 1e-10
     tree.free(); ctx.close()
+
+
+def test_program_budget_of_one_drops_every_fork_and_repeats():
+    """max_programs = 1: every cohort key of level 1 is dropped, so run() leaves through the `no jobs` exit right after the
+    scatter.  Two runs back to back must report the same dropped lanes and leave identical statistics (the second run's reset
+    of the routing tables on torch's stream must not overtake the first run's scatter on the context's stream)."""
+    import torch
+    from qsb200.cohorts import CohortTree
+    ntraj = 2000
+    ctx, tree, stats, per = _tree(ntraj)
+    tree.free()
+    tree = CohortTree(ctx, tree.schedule, max_programs=1)
+    rows = []
+    for _ in range(3):
+        stats.t.zero_(); per.zero_()
+        torch.cuda.synchronize()
+        info = tree.run()
+        ctx.sync()
+        assert info["levels"] == 1 and info["programs"] == 1 and info["dropped"] > 0 and info["lanes_rerun"] == 0
+        rows.append((info["dropped"], stats.t.cpu().numpy().copy()))
+    assert rows[0][0] == rows[1][0] == rows[2][0]
+    assert np.array_equal(rows[0][1], rows[1][1]) and np.array_equal(rows[0][1], rows[2][1])
+    # the lanes that were dropped are exactly the lanes with at least one failed purification
+    full_ctx, full, fstats, fper = _tree(ntraj)
+    fstats.t.zero_(); fper.zero_(); torch.cuda.synchronize()
+    finfo = full.run(); full_ctx.sync()
+    assert rows[0][0] == finfo["lanes_per_level"][1]
+    full.free(); full_ctx.close()
+    tree.free(); ctx.close()
+
+
+def test_levels_with_global_arena_programs_run_job_by_job(monkeypatch):
+    """A program too large for a shared-memory tile keeps its arena in global memory, and that executor instantiation takes one
+    job per launch.  A tree level with several such jobs used to fail ("does not fit in shared memory"); now each goes out as its
+    own launch pair.  QSB_EXEC_GLOBAL=1 (read at qsb_record_end) forces the placement for every program of a small tree; the
+    statistics must equal the shared-memory tree's bit for bit."""
+    import torch
+    ntraj = 3000
+    ctx, tree, stats, per = _tree(ntraj)
+    stats.t.zero_(); per.zero_(); torch.cuda.synchronize()
+    info = tree.run(); ctx.sync()
+    want, want_per = stats.t.cpu().numpy().copy(), per.cpu().numpy().copy()
+    assert tree.root.program.info()["global_arena"] == 0 and max(info["jobs_per_level"]) > 1
+    tree.free(); ctx.close()
+    monkeypatch.setenv("QSB_EXEC_GLOBAL", "1")
+    ctx, tree, stats, per = _tree(ntraj)
+    stats.t.zero_(); per.zero_(); torch.cuda.synchronize()
+    info2 = tree.run(); ctx.sync()
+    assert tree.root.program.info()["global_arena"] == 1
+    assert all(n.program.info()["global_arena"] == 1 for n in tree.nodes)
+    assert info2["jobs_per_level"] == info["jobs_per_level"] and info2["lanes_per_level"] == info["lanes_per_level"]
+    assert np.array_equal(stats.t.cpu().numpy(), want)
+    assert np.array_equal(per.cpu().numpy(), want_per)
+    tree.free(); ctx.close()

@@ -113,3 +113,34 @@ def test_one_trajectory_program_and_empty_lane_subset():
         rec.program.run_lanes(lanes.data_ptr(), 0, keep_stats=True); c.sync()       # zero lanes: nothing changes
         assert np.array_equal(stats.t.cpu().numpy()[:, :3], want[:, :3])
         rec.program.free(); c.close()
+
+
+def test_dense_operator_observable_on_tableau_states_is_a_pauli_expansion():
+    """observable(::MixedDestabilizer, indices, ::Operator), src/backends/clifford/express.jl:22-46: the k-qubit operator is expanded
+    in Pauli strings, every term one tableau expectation accumulated per trajectory (the accumulation is done on the host from
+    blocking copies -- the device row is rewritten by the next term on another stream)."""
+    import warnings
+    from qsb200 import ops
+    from qsb200 import symbols as S
+    from qsb200.backend import BatchContext, CudaBatchRepr
+    from qsb200.registers import Register, apply, initialize, observable, uptotime
+    ctx = BatchContext(1000, seed=0xDE25)
+    try:
+        reg = Register(2, CudaBatchRepr(ctx, "clifford"), S.Depolarization(2.0))
+        initialize(reg[1:2], ops.StabilizerState("XX ZZ"))
+        bell = np.array([1, 0, 0, 1]) / np.sqrt(2)
+        proj = np.outer(bell, bell.conj())                        # |Phi+><Phi+| = (II + XX - YY + ZZ) / 4: four terms share one device row
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            assert abs(complex(observable(reg[1:2], proj)) - 1.0) < 1e-12
+            uptotime(reg[1], 0.5); uptotime(reg[2], 0.5)          # Pauli noise: lanes now differ
+            st = reg.staterefs[0].state
+            got = st.observable([1, 2], proj, per_trajectory=True)
+            terms = [st.observable([1, 2], ops.Gate(p, S.tensor(*[{"X": S.X, "Y": S.Y, "Z": S.Z}[c] for c in p]), p), per_trajectory=True).values()
+                     for p in ("XX", "YY", "ZZ")]
+        want = (1 + terms[0] - terms[1] + terms[2]) / 4
+        assert np.max(np.abs(got.values() - want)) < 1e-12
+        assert 0.05 < 1 - got.mean < 0.6                           # some lanes were hit, not all
+        assert set(np.round(got.values().real, 12)) <= {0.0, 1.0}  # a Bell projector on a Bell-diagonal stabilizer state
+    finally:
+        ctx.close()
