@@ -505,6 +505,31 @@ def parity_check_tree(g, cpu, n):
     return res
 
 
+def censor_bias_check(g, workload, n):
+    """Untimed: what the fork budget costs in the STATISTICS.  The first n trajectory ids run through the GPU tree under the
+    benchmarked fork budget and through the compiled CPU replay with NO budget (every trajectory to the end of its own history,
+    the reference's semantics, examples/firstgenrepeater_lowlevel/setup.jl:209-237).  A censored lane leaves the GPU's rows at its
+    next disagreement, so later sampling points average over the survivors only; the difference of the ensemble means is that bias."""
+    import torch
+    free = cpu_compiled(workload, n, None)
+    assert free["censored"] == 0 and free["complete"] == n
+    with torch.cuda.stream(g.stream):
+        g.stats.t.zero_()
+        info = g.tree.run(traj_shift=0, nlanes=n)
+    g.stream.synchronize(); torch.cuda.synchronize()
+    rg, rf = g.stats.t[: g.nobs].cpu().numpy()[:, :3], free["rows"][: g.nobs]
+    both = (rg[:, 0] > 0) & (rf[:, 0] > 0)
+    mg, mf = rg[both, 1] / rg[both, 0], rf[both, 1] / rf[both, 0]
+    d = np.abs(mg - mf)
+    i = int(d.argmax())
+    return {"trajectories": n, "censored_gpu": info["censored"], "uncensored_op_lists": free["nodes"],
+            "against": "oracle/qsb_replay.c without a fork budget (every trajectory to the end of its own history) on the same trajectory ids",
+            "max_abs_diff_of_ensemble_means": float(d.max()), "rms_diff_of_ensemble_means": float(np.sqrt((d ** 2).mean())), "at_row": int(np.flatnonzero(both)[i]),
+            "mean_gpu_censored": float(mg[i]), "mean_uncensored": float(mf[i]),
+            "max_alive_count_diff": float(np.abs(rg[:, 0] - rf[:, 0]).max()),
+            "standard_error_of_a_mean_at_this_n": float(1.0 / np.sqrt(n))}
+
+
 def run_gpu_workload(workload, ntraj, steps, warmup, rank, world, local_rank, profile=True, mode="per_op", cohort_depth=3, chunks=1, check=True, keep=None):
     """mode "per_op": every backend call is one launch (the drop-in path, host schedule re-run each step).
     mode "program": the schedule is recorded once (untimed, reported as record_ms) and each step replays it as ONE fused
@@ -668,20 +693,30 @@ def fused_roofline(out, rows, g, workload, lanes, peak, which, clocks):
     inst = dram = 0.0
     have = True
     per_kernel = {}
+    base = workload.replace("_masks", "").replace("_cohort", "")
+    wave_facts = True
     for r in fused:
-        f = ncu_facts(workload.replace("_masks", "").replace("_cohort", ""), r["kernel"])
-        if not f:
-            have = False
-            continue
-        scale = lane_runs / f["trajectories"]          # instructions and bytes scale with the lanes processed
+        # a cohort tree has captures of its own wave launches (summed over the levels of one step: the re-runs are inside); otherwise
+        # the single-program capture is scaled by the lane-runs of the step
+        f = ncu_facts(base + "_cohort", r["kernel"]) if "ensemble" in out else None
+        if f:
+            scale = lanes / f["trajectories"]
+        else:
+            wave_facts = False
+            f = ncu_facts(base, r["kernel"])
+            if not f:
+                have = False
+                continue
+            scale = lane_runs / f["trajectories"]      # instructions and bytes scale with the lanes processed
         inst += f["warp_inst"] * scale; dram += f["dram_bytes"] * scale
         per_kernel[r["kernel"]] = {"ms": r["ms"], "issue_frac": f["warp_inst"] * scale / (sms * 4 * sm_hz * r["ms"] * 1e-3),
                                    "ncu": {k: f[k] for k in ("grid", "block", "issue_active", "source") if k in f}}
     issue_peak = sms * 4 * sm_hz                       # warp instructions per second the device can issue
     facts_commit, facts_changed = ncu_facts_provenance([r["kernel"] for r in fused])
     blk = {"modelled": True,
-           "source": f"kernel time: CUDA events in this run; warp instructions and DRAM bytes: ncu captures of the single-program launch at commit {facts_commit} "
-                     "(profiles/ncu_kernels.json), scaled linearly by lanes processed -- the multi-job wave launches of a cohort tree were not captured themselves",
+           "source": f"kernel time: CUDA events in this run; warp instructions and DRAM bytes: ncu captures at commit {facts_commit} (profiles/ncu_kernels.json) of "
+                     + ("the tree's own wave launches, summed over the levels of one 10^6-lane step" if ("ensemble" in out and wave_facts and have)
+                        else "the single-program launch, scaled linearly by the lanes processed"),
            "facts_stale": facts_changed or None,       # kernel source files edited since the capture: the counts may no longer describe this build
            "bound": "issue", "kernel": kname, "unit": "warp-inst/s", "peak": issue_peak, "peak_source": f"{sms} SMs x 4 schedulers x {sm_hz / 1e6:.0f} MHz (SM clock sampled under load)",
            "achieved": inst / sec if have else None, "frac": inst / sec / issue_peak if have else None,
@@ -713,7 +748,7 @@ def _headline(full: dict) -> dict:
     """The compact record for stdout (<= HEADLINE_MAX_BYTES).  The full record (kernel tables, per-workload extras, logs) goes to
     the side file named in `details`.  Long prose is cut, then optional keys are dropped, until the line fits."""
     keys = ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype", "data",
-            "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline", "parity_check", "ensemble", "state_ops_per_sec",
+            "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline", "parity_check", "censor_bias", "ensemble", "state_ops_per_sec",
             "useful_state_ops_per_sec", "cpu_baseline_optimised", "alive_at_end_fraction", "extra", "details")
     line = {k: full[k] for k in keys if k in full}
     if isinstance(line.get("config"), dict):
@@ -730,6 +765,9 @@ def _headline(full: dict) -> dict:
             line[k] = {kk: _short(v, 220) for kk, v in line[k].items() if kk != "note"}
     if isinstance(line.get("parity_check"), dict):
         line["parity_check"] = {k: _short(v, 100) for k, v in line["parity_check"].items()}
+    if isinstance(line.get("censor_bias"), dict):
+        line["censor_bias"] = {k: _short(v, 60) for k, v in line["censor_bias"].items()
+                               if k in ("trajectories", "censored_gpu", "max_abs_diff_of_ensemble_means", "rms_diff_of_ensemble_means", "uncensored_op_lists", "error")}
     if isinstance(line.get("ensemble"), dict):
         e = line["ensemble"]
         line["ensemble"] = {k: e[k] for k in ("complete_fraction", "censored_fraction", "lane_runs_per_trajectory", "programs", "levels", "max_forks_per_trajectory",
@@ -829,7 +867,7 @@ def main():
     kept = []
     main_res = run_gpu_workload(args.workload, ntraj, args.steps, args.warmup, rank, world, local_rank, mode=mode, cohort_depth=args.cohort_depth, chunks=args.chunks,
                                 keep=kept if (mode == "cohort" and rank == 0 and world == 1 and not args.no_cpu) else None)
-    cpu = cpu_py = None
+    cpu = cpu_py = censor_bias = None
     parity = main_res.get("parity_check")
     if rank == 0 and not args.no_cpu and CPU_SAMPLE.get(args.workload, (0, 0))[0]:
         # rank 0 at every N (same sample, all host cores), so that each line carries its own same-run CPU denominator
@@ -839,6 +877,10 @@ def main():
             n = 4096
             c = cpu_compiled(args.workload, n, args.cohort_depth, tree=craw["tree"])
             parity = parity_check_tree(kept[0], c, n)
+            try:
+                censor_bias = censor_bias_check(kept[0], args.workload, 2048)
+            except Exception as e:   # a diagnostic: it must not take the headline down
+                censor_bias = {"error": repr(e)[:200]}
     for g in kept:
         g.tree.free(); g.ctx.close()
     extra = {}
@@ -875,7 +917,7 @@ def main():
                                  "cohort": "wall clock around the whole tree run: launches, per-level cohort routing (D2H of cohort keys and sizes, H2D of the job tables; the recorded "
                                            "programs stay resident on the device), all-reduce + D2H of the step's statistics",
                                  "per_op": "wall clock around the public API calls incl. the all-reduce + D2H of the step's statistics; inputs are host-side symbols/matrices passed by value through the C-ABI"}[mode]},
-                "program": main_res.get("program"), "parity_check": parity, "ensemble": main_res.get("ensemble"),
+                "program": main_res.get("program"), "parity_check": parity, "censor_bias": censor_bias, "ensemble": main_res.get("ensemble"),
                 "alive_at_end_fraction": main_res.get("alive_at_end_fraction"),
                 "gpu_launches": int(main_res["launches_per_step"] * args.steps),
                 "state_ops_per_sec": main_res["ops_per_step"] * world / (main_res["dev_ms_per_step"] * 1e-3),
